@@ -1,0 +1,214 @@
+/*
+ * lmpc.h — C ABI of the B200-native batched convex-MPC engine (liblmpc.so).
+ *
+ * This is the drop-in boundary for ONE hot path of zha0ming1e/legged_mpc_control:
+ * legged_ctrl's convex MPC (SRBD model build -> discretise -> condense -> dense QP ->
+ * first-step 4x3 ground reaction forces).  Every entry point names the reference
+ * interface it replaces (paths relative to /root/reference/src/legged_ctrl/).
+ *
+ *   reference seam                                            replaced by
+ *   ------------------------------------------------------    -------------------------
+ *   ConvexQPSolver::ConvexQPSolver(q,r)                        lmpc_create
+ *       src/mpc_ctrl/convex_mpc/ConvexQPSolver.cpp:16-196
+ *   ConvexQPSolver::calc_mpc_reference(state, leg_FSM)         lmpc_solve (stage 1: refs,
+ *       ConvexQPSolver.cpp:254-313                                A_d/B_d, bounds)
+ *   ConvexQPSolver::update_cons_matrix()                       lmpc_solve (stage 2: condense)
+ *       ConvexQPSolver.cpp:230-239
+ *   ConvexQPSolver::compute_grfs(state) -> Matrix<12,1>        lmpc_solve (stage 3: QP) -> grf
+ *       ConvexQPSolver.cpp:314-327
+ *   LeggedContactFSM::predict_contact_state(dt)                lmpc_gait_contact_table
+ *       src/utils/LeggedContactFSM.cpp:280-294 (+ tables :93-212)
+ *   OSQP warm start (ConvexQPSolver.cpp:185)                   lmpc_reset_warm_start
+ *   ~ConvexQPSolver                                            lmpc_destroy
+ *
+ * Plain pointers and sizes only; no C++/torch types cross this boundary.  All matrices are
+ * column-major so that Eigen::Matrix<double,R,C>::data() can be passed unchanged.
+ * No CPU fallback exists behind this ABI: if no CUDA device is usable, lmpc_create fails.
+ */
+#ifndef LMPC_H_
+#define LMPC_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LMPC_ABI_VERSION 1
+#define LMPC_MAX_HORIZON 32 /* reference PLAN_HORIZON is 30 (include/LeggedParams.h:13) */
+#define LMPC_NUM_LEG 4      /* include/LeggedParams.h:19, order FL FR RL RR */
+#define LMPC_STATE_DIM 12   /* MPC_STATE_DIM_SPARSE, include/LeggedParams.h:15 */
+#define LMPC_INPUT_DIM 12   /* DIM_GRF, include/LeggedParams.h:21 */
+
+typedef enum lmpc_status {
+  LMPC_OK = 0,
+  LMPC_ERR_INVALID_ARG = 1,
+  LMPC_ERR_CUDA = 2,
+  LMPC_ERR_NO_DEVICE = 3,
+  LMPC_ERR_NOT_CONVERGED = 4, /* >=1 problem of the batch ended with status != 0 (grf = 0 for it) */
+  LMPC_ERR_ALLOC = 5
+} lmpc_status;
+
+/* per-problem status codes written to lmpc_batch_out.status */
+enum {
+  LMPC_PROB_OK = 0,          /* exact active-set solution, KKT verified on device */
+  LMPC_PROB_OK_IPM_ONLY = 1, /* converged by interior point to tight tolerance, no exact polish */
+  LMPC_PROB_MAX_ITER = 2,    /* not converged: grf zeroed (reference NaN rule, ConvexQPSolver.cpp:321-326) */
+  LMPC_PROB_NON_FINITE = 3   /* non-finite input or iterate: grf zeroed */
+};
+
+enum { LMPC_DISC_EULER = 0, LMPC_DISC_ZOH = 1 };
+/* REF_HALF: 1/2 z'Pz + q'z as the reference hands it to OSQP (ConvexQPSolver.cpp:29-50,308).
+ * NS_TWO:   H = 2(B'LB + aK), g = 2B'L(Ax0 - xref): same minimiser, multipliers scale by 2. */
+enum { LMPC_COST_REF_HALF = 0, LMPC_COST_NS_TWO = 1 };
+enum { LMPC_PREC_F64 = 0, LMPC_PREC_F32 = 1 };
+enum { LMPC_SOLVER_IPM = 0, LMPC_SOLVER_ACTIVE_SET = 1 };
+
+typedef struct lmpc_params {
+  int32_t horizon;            /* H in [1, LMPC_MAX_HORIZON]; reference: 30 (LeggedParams.h:13) */
+  int32_t discretisation;     /* LMPC_DISC_*; reference: EULER (ConvexQPSolver.cpp:211,227) */
+  int32_t cost_scaling;       /* LMPC_COST_* */
+  int32_t xref_index_offset;  /* x_{k+1} tracks pose at (k+offset)*dt; reference: 0 (ConvexQPSolver.cpp:267-269) */
+  int32_t precision;          /* LMPC_PREC_* */
+  int32_t solver;             /* LMPC_SOLVER_* */
+  int32_t max_iter;           /* interior-point iteration cap; 0 -> default (40) */
+  int32_t reserved0;
+  double dt;                  /* reference: MPC_UPDATE_FREQUENCY/1000 = 0.01 (ConvexQPSolver.cpp:26) */
+  double mu;                  /* friction coefficient; reference: 0.3 (ConvexQPSolver.cpp:25) */
+  double fz_max;              /* reference: 180 (ConvexQPSolver.cpp:171,336,341) */
+  double mass;                /* param.robot_mass (LeggedState.cpp:146) */
+  double gravity;             /* reference: 9.8 (ConvexQPSolver.cpp:175,296) */
+  double active_tol;          /* |row residual| <= active_tol [N] marks a row active; 0 -> 1e-6 */
+  double inertia[9];          /* body-frame trunk inertia, column-major (symmetric) (LeggedState.cpp:150-164) */
+  double q[13];               /* state weights, order [rpy, pos, omega, vel, (gravity state, ignored)] */
+  double r[12];               /* force weights */
+} lmpc_params;
+
+/* Batch inputs, structure-of-arrays, problem-major contiguous.  Every array holds one
+ * fixed-size record per problem; `on_device` says whether the pointers are host or device
+ * pointers (all of one kind).  Field sources in the reference (LeggedState.h):
+ *   x0           [B][12]  fbk.root_euler, root_pos, root_ang_vel, root_lin_vel  (:27-33; packed
+ *                         as ConvexQPSolver.cpp:256-259)
+ *   rot          [B][9]   fbk.root_rot_mat, column-major                         (:30)
+ *   foot_pos_abs [B][12]  fbk.foot_pos_abs, 3x4 column-major                     (:52)
+ *   cmd          [B][9]   ctrl.root_euler_d[0], root_euler_d[1], root_pos_d[2],
+ *                         root_lin_vel_d_rel[0..2], root_ang_vel_d_rel[0..2]     (:79-85)
+ *   contact      [B][H][4] uint8; row 0 = ctrl.plan_contacts (:96), row i>0 =
+ *                         leg_FSM[j].predict_contact_state(i*dt) (ConvexQPSolver.cpp:329-346)
+ * Optional per-problem overrides (NULL -> value from lmpc_params):
+ *   q [B][12], r [B][12], mu [B], fz_max [B], mass [B], inertia [B][9]
+ */
+typedef struct lmpc_batch_in {
+  const double* x0;
+  const double* rot;
+  const double* foot_pos_abs;
+  const double* cmd;
+  const uint8_t* contact;
+  const double* q;
+  const double* r;
+  const double* mu;
+  const double* fz_max;
+  const double* mass;
+  const double* inertia;
+  int32_t on_device;
+  int32_t reserved0;
+} lmpc_batch_in;
+
+/* Number of 32-bit words of the per-problem active-set bitmask.  Bit layout follows the
+ * reference's row order (ConvexQPSolver.cpp:131-177) with the two-sided f_z row split:
+ *   bit 16k + 4*leg + {0,1,2,3}  friction rows  0<=fx+mu fz, fx-mu fz<=0, 0<=fy+mu fz, fy-mu fz<=0
+ *   bit 16H + 4k + leg           f_z at its lower bound (0)
+ *   bit 20H + 4k + leg           f_z at its upper bound (fz_max * contact)
+ * A row is "active" when its residual is within params.active_tol. */
+#define LMPC_ACTIVE_WORDS(H) ((24 * (H) + 31) / 32)
+
+/* Batch outputs; any pointer except grf may be NULL.
+ *   grf        [B][12]  u_0, leg-major xyz == Eigen::Matrix<double,3,4> column-major
+ *                       (ConvexQPSolver.cpp:320-326; ConvexMpc.cpp:73-75)
+ *   status     [B]      LMPC_PROB_*
+ *   iters      [B]      low 16 bits: factorizations (interior-point iterations + active-set
+ *                       polish solves); high 16 bits: polish solves only
+ *   active_set [B][LMPC_ACTIVE_WORDS(H)]
+ *   U          [B][12H] full horizon solution u_0..u_{H-1}
+ */
+typedef struct lmpc_batch_out {
+  double* grf;
+  int32_t* status;
+  int32_t* iters;
+  uint32_t* active_set;
+  double* U;
+  int32_t on_device;
+  int32_t reserved0;
+} lmpc_batch_out;
+
+typedef struct lmpc_handle lmpc_handle;
+
+/* Fill `p` with a named preset: "reference_a1" (H=30, dt=0.01, Euler, A1 sim yaml weights —
+ * config/gazebo_a1_convex.yaml:40-72,133-140), "reference_go1", "northstar_a1" (H=10,
+ * dt=0.025, ZOH, NS_TWO), "northstar_go1_h20".  Returns LMPC_ERR_INVALID_ARG if unknown. */
+lmpc_status lmpc_params_preset(const char* name, lmpc_params* p);
+
+/* Replaces the ConvexQPSolver constructor (ConvexQPSolver.cpp:16-196).  `device` is a CUDA
+ * ordinal; the handle owns device workspaces and pinned staging sized for `max_batch`. */
+lmpc_status lmpc_create(const lmpc_params* params, int32_t max_batch, int32_t device,
+                        lmpc_handle** out);
+
+/* Replaces calc_mpc_reference + update_cons_matrix + compute_grfs (ConvexMpc.cpp:70-72) for
+ * `batch` independent robots.  Blocking.  Returns LMPC_ERR_NOT_CONVERGED if any problem failed
+ * (its grf is zero, as the reference returns zeros on NaN); outputs are valid either way. */
+lmpc_status lmpc_solve(lmpc_handle* h, int32_t batch, const lmpc_batch_in* in,
+                       const lmpc_batch_out* out);
+
+/* Asynchronous variant on the handle's stream (or `cuda_stream` if non-NULL: a cudaStream_t).
+ * Only valid with on_device inputs and outputs.  lmpc_wait blocks until it is done. */
+lmpc_status lmpc_solve_async(lmpc_handle* h, int32_t batch, const lmpc_batch_in* in,
+                             const lmpc_batch_out* out, void* cuda_stream);
+lmpc_status lmpc_wait(lmpc_handle* h);
+
+/* Forget the device-resident warm start (OSQP warm start analogue, ConvexQPSolver.cpp:185). */
+lmpc_status lmpc_reset_warm_start(lmpc_handle* h);
+
+void lmpc_destroy(lmpc_handle* h);
+
+/* Thread-local, never NULL. */
+const char* lmpc_last_error_string(void);
+
+int32_t lmpc_abi_version(void);
+
+/* Kernel launches issued by this handle since creation (bench evidence). */
+int64_t lmpc_launch_count(const lmpc_handle* h);
+
+/* Device time in ms of the most recent lmpc_solve/lmpc_solve_async kernel sequence, measured
+ * with CUDA events on the stream it ran on (valid after lmpc_wait / blocking solve). */
+float lmpc_last_kernel_ms(const lmpc_handle* h);
+
+/* Mean reduced QP dimension and factorizations per problem of the last solve (for the
+ * algorithmic-FLOP count). */
+lmpc_status lmpc_last_stats(const lmpc_handle* h, double* mean_n_eff, double* mean_factorizations,
+                            double* flops_executed);
+
+/* ---- gait schedule (host side; replaces LeggedContactFSM::predict_contact_state) ---- */
+enum {
+  LMPC_GAIT_TROT = 0,            /* LeggedContactFSM.cpp:93-114  */
+  LMPC_GAIT_TROT_WITH_STAND = 1, /* :116-157 */
+  LMPC_GAIT_CRAWL = 2,           /* :158-199 */
+  LMPC_GAIT_STAND = 3,           /* :201-212 */
+  LMPC_GAIT_BOUND = 4,           /* not in the reference: front pair / rear pair in antiphase */
+  LMPC_GAIT_PRONK = 5            /* not in the reference: all legs in phase, duty 0.5 */
+};
+
+/* Contact state of `leg` at gait phase `phase` advanced by gait_speed*delta_t, following
+ * LeggedContactFSM.cpp:280-294 (wrap by repeated -1 while > 1; first switch_time >= phase). */
+int32_t lmpc_gait_predict_contact(int32_t gait, int32_t leg, double phase, double gait_speed,
+                                  double delta_t);
+
+/* Fill contact[B][H][4] from per-robot gait type, per-leg phase [B][4] and gait speed [B]:
+ * row i uses predict_contact(i*dt) (row 0 = current planned contact, i.e. delta_t = 0). */
+lmpc_status lmpc_gait_contact_table(int32_t batch, int32_t horizon, double dt, const int32_t* gait,
+                                    const double* phase, const double* gait_speed,
+                                    uint8_t* contact);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LMPC_H_ */
