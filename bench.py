@@ -1,0 +1,294 @@
+#!/usr/bin/env python
+"""bench.py — convex-MPC QP solves/s (BASELINE.json metric) on N B200s of one node.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+
+A "step" is one pass of the hot path (SRBD build -> discretise -> condense -> QP -> GRF) over one
+batch of 65 536 synthetic A1 trot problems, H=10 (the configuration the metric is quoted on).
+`value` is device-resident throughput (inputs already in HBM), `e2e` goes through the public
+host-buffer API (H2D + solve + D2H per step).  N>1: launched by torch.distributed.run, one
+process per GPU; each rank owns its own 65 536-problem shard of the stream (weak scaling), no
+data-path collective; time = max over ranks.  Prints ONE JSON line on rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+from legged_mpc_control_b200 import abi, presets, synth  # noqa: E402
+
+METRIC = "convex_mpc_qp_solves_per_sec"
+UNIT = "solves/s"
+PRESET = "northstar_a1"
+BATCH = 65536
+SEED = 3
+L2_FLUSH_BYTES = 256 << 20
+
+
+def workload_config(n_gpus, batch):
+    p = presets.preset(PRESET)
+    return {
+        "workload": f"a1_trot_h{p.horizon}_dt{p.dt}_batch{batch}_seed{SEED}",
+        "preset": PRESET, "horizon": p.horizon, "dt": p.dt, "batch_per_gpu": batch,
+        "global_batch": batch * n_gpus, "parallelism": f"batch-shard x{n_gpus} (no collective)",
+        "l2": "flushed between timed steps (256 MiB write)",
+    }
+
+
+# ------------------------------------------------------------------ CPU arm (oracle port)
+def cpu_sample(p, seconds_target=12.0, threads=None):
+    """Times the oracle (the CPU restatement of the reference path; kind 'port') on a bounded
+    sample of the same workload with all host threads.  Returns (solves/s, cores, sample str)."""
+    from oracle import binding as ob
+    ob.build()
+    threads = threads or (os.cpu_count() or 1)
+    pilot_n = 32 * threads
+    b = synth.make_batch(pilot_n, p.horizon, p.dt, seed=SEED)
+    t0 = time.perf_counter()
+    ob.solve_batch(p, b, eliminate_swing=True, nthreads=threads, want_kkt=False)
+    pilot = time.perf_counter() - t0
+    n = int(min(BATCH, max(pilot_n, pilot_n * seconds_target / max(pilot, 1e-3))))
+    b = synth.make_batch(n, p.horizon, p.dt, seed=SEED)
+    t0 = time.perf_counter()
+    out = ob.solve_batch(p, b, eliminate_swing=True, nthreads=threads, want_kkt=False)
+    dt = time.perf_counter() - t0
+    assert out["failures"] == 0
+    return n / dt, threads, f"first {n} problems of the workload stream, {threads} threads, one problem per thread, {dt:.1f} s"
+
+
+def run_reference(args):
+    """--impl reference: the reference's own implementation of this path cannot be built here
+    (Eigen + OSQP + ROS are absent), so this arm times the oracle port on the
+    host cores: rank 0 only."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    p = presets.preset(PRESET)
+    vals = []
+    sample = ""
+    cores = os.cpu_count() or 1
+    for i in range(args.warmup + args.steps):
+        v, cores, sample = cpu_sample(p, seconds_target=max(2.0, 60.0 / (args.warmup + args.steps)))
+        if i >= args.warmup:
+            vals.append(v)
+    val = float(np.mean(vals))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * BATCH / val,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic", "config": workload_config(args.gpus, BATCH),
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------ clocks sampler
+class ClockSampler(threading.Thread):
+    FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                r = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits"],
+                                   capture_output=True, text=True, timeout=5)
+                parts = [x.strip() for x in r.stdout.strip().split(",")]
+                if len(parts) >= 6:
+                    self.samples.append(parts)
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        mhz = sorted(int(s[0]) for s in self.samples if s[0].isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(s[2 + i].lower().startswith("active") for s in self.samples)]
+        return {"sm_mhz": mhz[len(mhz) // 2] if mhz else None,
+                "sm_max_mhz": int(self.samples[0][1]) if self.samples[0][1].isdigit() else None,
+                "reasons": reasons, "samples": len(self.samples)}
+
+
+# ------------------------------------------------------------------ GPU arm
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from legged_mpc_control_b200.engine import ConvexMpcEngine, microbench_fp64
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    p = presets.preset(PRESET)
+    H, B = p.horizon, args.batch
+    # weak scaling: rank r solves problems [r*B, (r+1)*B) of the stream
+    batch = synth.make_batch(B, H, p.dt, seed=SEED, start=rank * B)
+    names = ("x0", "rot", "foot_pos_abs", "cmd", "contact")
+    tin = {k: torch.from_numpy(batch[k]).to(dev) for k in names}
+    W = abi.active_words(H)
+    tout = {"grf": torch.zeros(B, 12, dtype=torch.float64, device=dev),
+            "status": torch.zeros(B, dtype=torch.int32, device=dev),
+            "iters": torch.zeros(B, dtype=torch.int32, device=dev),
+            "active_set": torch.zeros(B, W, dtype=torch.int32, device=dev)}
+    pin = {k: v.data_ptr() for k, v in tin.items()}
+    pout = {k: v.data_ptr() for k, v in tout.items()}
+    eng = ConvexMpcEngine(p, B, device=local)
+    flush = torch.empty(L2_FLUSH_BYTES // 4, dtype=torch.int32, device=dev)
+    ts = torch.cuda.Stream(device=dev)  # the stream the kernels are launched on AND the events are recorded on
+    stream = ts.cuda_stream
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def device_step():
+        eng.solve_device(pin, pout, B, stream=stream, wait=True)
+
+    for _ in range(args.warmup):
+        device_step()
+    sampler = ClockSampler(local)
+    sampler.start()
+    barrier()
+    n0 = eng.launch_count
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    kern_ms = []
+    with torch.cuda.stream(ts):
+        for i in range(args.steps):
+            flush.fill_(i)  # L2 flush between timed iterations (outside the event pair)
+            ev[i][0].record(ts)
+            device_step()
+            ev[i][1].record(ts)
+            kern_ms.append(eng.last_kernel_ms)
+    barrier()
+    launches = eng.launch_count - n0
+    total_ms = sum(a.elapsed_time(b) for a, b in ev)
+    stats = eng.last_stats()
+    bad = int((tout["status"] > 1).sum().item())
+    t = torch.tensor([total_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total_ms = float(t.item())
+    value = world * B * args.steps / (total_ms * 1e-3)
+
+    # ---- e2e: public host-buffer API, pinned host memory, H2D + D2H inside the timed region
+    hb = {k: torch.from_numpy(batch[k]).pin_memory().numpy() for k in names}
+    for _ in range(max(1, args.warmup // 2)):
+        eng.compute_grfs(hb, want_U=False)
+    barrier()
+    t0 = time.perf_counter()
+    e2e_steps = max(3, min(args.steps, 10))
+    for _ in range(e2e_steps):
+        out = eng.compute_grfs(hb, want_U=False)
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_val = world * B * e2e_steps / float(te.item())
+    h2d = sum(hb[k].nbytes for k in names)
+    d2h = out["grf"].nbytes + out["status"].nbytes + out["iters"].nbytes + out["active_set"].nbytes
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
+
+    # ---- final result gather (the only exchange the path has; outside the timed region)
+    if world > 1:
+        from legged_mpc_control_b200 import shard
+        g = shard.gather_results(tout["grf"], world * B, rank, world)
+        if rank == 0:
+            assert g.shape[0] == world * B
+
+    if rank == 0:
+        # roofline: executed FP64 flops of the dominant kernel / its launch duration
+        peaks = {}
+        for name, kind in (("dfma", 0), ("dmma_m8n8k4", 1), ("dmma_m16n8k4", 2), ("dmma_m16n8k8", 3), ("dmma_m16n8k16", 4)):
+            try:
+                peaks[name] = microbench_fp64(kind, device=local, reps=3)
+            except Exception as e:  # pragma: no cover
+                peaks[name] = None
+        peak = max(v for v in peaks.values() if v)
+        kms = float(np.mean(kern_ms))
+        achieved = stats["flops_executed"] / (kms * 1e-3) / 1e12
+        n = 12 * H
+        Kf = stats["mean_factorizations"]
+        f_alg_dense = 1728 * H * (H - 1) + 3456 * H * (H + 1) * (H + 2) / 6 + (2 * n * n + 24 * n) + Kf * (n ** 3 / 3 + 4 * n * n)
+        io_bytes = B * (h2d / B + 12 * 8 + 4 + 4 + 4 * W)
+        cpu_val, cores, sample = cpu_sample(p)
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(world, B),
+            "p50_batch_latency_ms": float(np.median([a.elapsed_time(b) for a, b in ev])),
+            "clocks": sampler.summary(),
+            "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                    "steps": e2e_steps, "api": "ConvexMpcEngine.compute_grfs -> lmpc_solve (host pointers)"},
+            "gpu_launches": int(launches),
+            "roofline": {
+                "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+                "traffic": None, "kernel": "lmpc::solve_kernel<64>", "kernel_ms": kms,
+                "precision": "fp64", "peak_source": "measured on this GPU by lmpc_microbench_fp64 (MEASURED_PEAKS.json has no FP64 entry)",
+                "fp64_peaks_tflops": peaks,
+                "flops_per_launch_executed": stats["flops_executed"], "mean_n_eff": stats["mean_n_eff"],
+                "mean_factorizations": Kf, "alg_flops_per_solve_dense_n12H": f_alg_dense,
+                "hbm": {"algorithmic_bytes_per_launch": io_bytes, "achieved_GBps": io_bytes / (kms * 1e-3) / 1e9,
+                        "peak_GBps": _hbm_peak()},
+            },
+            "cpu_baseline": {"value": cpu_val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "not_converged": bad,
+        }
+        print(json.dumps(line), flush=True)
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def _hbm_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return json.load(f)["hbm_gbs"]
+    except Exception:
+        return 6650.0  # fallback stated in B200_PROFILING.md
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=BATCH)
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "b200":
+        args.warmup = 3  # timing rule: W >= 3
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

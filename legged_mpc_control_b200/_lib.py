@@ -1,0 +1,59 @@
+"""Loader for the in-tree CUDA library liblmpc.so.  There is no fallback: if the library is
+missing or cannot be loaded the import of anything that computes fails loudly."""
+import ctypes as C
+import os
+
+from . import abi
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "liblmpc.so")
+_LIB = None
+
+EXPORTS = (
+    "lmpc_params_preset", "lmpc_create", "lmpc_solve", "lmpc_solve_async", "lmpc_wait",
+    "lmpc_reset_warm_start", "lmpc_destroy", "lmpc_last_error_string", "lmpc_abi_version",
+    "lmpc_launch_count", "lmpc_last_kernel_ms", "lmpc_last_stats", "lmpc_gait_predict_contact",
+    "lmpc_gait_contact_table", "lmpc_microbench_fp64",
+)
+
+
+class LmpcLibraryMissing(RuntimeError):
+    pass
+
+
+def lib():
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    if not os.path.exists(LIB_PATH):
+        raise LmpcLibraryMissing(
+            f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc, sm_100a).  This package has no CPU or PyTorch fallback.")
+    L = C.CDLL(LIB_PATH)
+    L.lmpc_last_error_string.restype = C.c_char_p
+    L.lmpc_abi_version.restype = C.c_int32
+    L.lmpc_launch_count.restype = C.c_int64
+    L.lmpc_launch_count.argtypes = [C.c_void_p]
+    L.lmpc_last_kernel_ms.restype = C.c_float
+    L.lmpc_last_kernel_ms.argtypes = [C.c_void_p]
+    L.lmpc_params_preset.argtypes = [C.c_char_p, C.POINTER(abi.LmpcParams)]
+    L.lmpc_create.argtypes = [C.POINTER(abi.LmpcParams), C.c_int32, C.c_int32, C.POINTER(C.c_void_p)]
+    L.lmpc_solve.argtypes = [C.c_void_p, C.c_int32, C.POINTER(abi.LmpcBatchIn), C.POINTER(abi.LmpcBatchOut)]
+    L.lmpc_solve_async.argtypes = [C.c_void_p, C.c_int32, C.POINTER(abi.LmpcBatchIn), C.POINTER(abi.LmpcBatchOut), C.c_void_p]
+    L.lmpc_wait.argtypes = [C.c_void_p]
+    L.lmpc_reset_warm_start.argtypes = [C.c_void_p]
+    L.lmpc_destroy.argtypes = [C.c_void_p]
+    L.lmpc_destroy.restype = None
+    L.lmpc_last_stats.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)]
+    L.lmpc_gait_predict_contact.argtypes = [C.c_int32, C.c_int32, C.c_double, C.c_double, C.c_double]
+    L.lmpc_gait_predict_contact.restype = C.c_int32
+    L.lmpc_gait_contact_table.argtypes = [C.c_int32, C.c_int32, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    L.lmpc_microbench_fp64.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_double)]
+    if L.lmpc_abi_version() != abi.ABI_VERSION:
+        raise LmpcLibraryMissing(f"liblmpc.so ABI {L.lmpc_abi_version()} != python binding {abi.ABI_VERSION}")
+    _LIB = L
+    return L
+
+
+def last_error() -> str:
+    return lib().lmpc_last_error_string().decode()

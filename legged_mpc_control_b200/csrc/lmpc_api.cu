@@ -1,0 +1,355 @@
+// lmpc_api.cu — kernels + C ABI of liblmpc.so (include/lmpc.h).  sm_100a only; there is no
+// CPU path behind this ABI: every entry point that computes needs a CUDA device.
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/lmpc.h"
+#include "lmpc_solver.cuh"
+
+namespace lmpc {
+
+// ---------------------------------------------------------------- kernels
+
+// Reduced dimension of every problem (3 per stance leg-step) and the batch maximum: sizes the
+// shared-memory plan of the solve launch.
+__global__ void classify_kernel(const uint8_t* __restrict__ contact, int H, int B,
+                                KStats* __restrict__ stats) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  int n = 0;
+  if (i < B) {
+    const uint8_t* c = contact + (size_t)(4 * H) * i;
+    for (int t = 0; t < 4 * H; ++t) n += c[t] ? 3 : 0;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) n = max(n, __shfl_xor_sync(0xffffffffu, n, o));
+  if ((threadIdx.x & 31) == 0 && n > 0) atomicMax(&stats->n_max, n);
+}
+
+// Persistent solve: one CTA per QP at a time, problems handed out by an atomic counter.
+template <int NT>
+__global__ void __launch_bounds__(NT) solve_kernel(const __grid_constant__ KParams P,
+                                                   const __grid_constant__ KBatch Bt,
+                                                   KStats* stats, int ncap, int mats_in_smem,
+                                                   double* gws, int* work_counter) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const SmemPlan pl = make_plan(P.H, ncap, mats_in_smem != 0);
+  double* gH = nullptr;
+  double* gM = nullptr;
+  if (!mats_in_smem) {
+    const size_t ps = (size_t)packed_size(ncap);
+    gH = gws + (size_t)blockIdx.x * 2 * ps;
+    gM = gH + ps;
+  }
+  int* si = reinterpret_cast<int*>(smem + pl.oINT);
+  for (;;) {
+    if (threadIdx.x == 0) si[INT_WORK] = atomicAdd(work_counter, 1);
+    __syncthreads();
+    const int w = si[INT_WORK];
+    __syncthreads();
+    if (w >= Bt.B) break;
+    const int pi = Bt.order ? Bt.order[w] : w;
+    solve_one<NT>(P, Bt, stats, pl, smem, gH, gM, pi);
+  }
+}
+
+}  // namespace lmpc
+
+// ---------------------------------------------------------------- host side
+
+using lmpc::KBatch;
+using lmpc::KParams;
+using lmpc::KStats;
+
+static thread_local std::string g_err = "";
+static void set_err(const std::string& s) { g_err = s; }
+extern "C" const char* lmpc_last_error_string(void) { return g_err.c_str(); }
+extern "C" int32_t lmpc_abi_version(void) { return LMPC_ABI_VERSION; }
+
+#define CK(call)                                                                              \
+  do {                                                                                        \
+    cudaError_t e_ = (call);                                                                  \
+    if (e_ != cudaSuccess) {                                                                  \
+      set_err(std::string(#call) + ": " + cudaGetErrorString(e_));                            \
+      return LMPC_ERR_CUDA;                                                                   \
+    }                                                                                         \
+  } while (0)
+
+static constexpr int kThreads = 64;
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  cudaError_t ensure(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e == cudaSuccess) cap = bytes;
+    return e;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+struct lmpc_handle {
+  lmpc_params params;
+  KParams kp;
+  int device = 0;
+  int max_batch = 0;
+  int num_sms = 0;
+  int smem_optin = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  // device staging for host-pointer calls
+  DevBuf d_x0, d_rot, d_foot, d_cmd, d_contact, d_q, d_r, d_mu, d_fz, d_mass, d_inertia;
+  DevBuf d_grf, d_status, d_iters, d_active, d_U;
+  DevBuf d_stats, d_counter, d_ws;
+  KStats last_stats;
+  float last_ms = 0.f;
+  int64_t launches = 0;
+  bool pending = false;
+  cudaStream_t pending_stream = nullptr;
+};
+
+static lmpc_status validate_params(const lmpc_params* p) {
+  if (!p) { set_err("params is NULL"); return LMPC_ERR_INVALID_ARG; }
+  if (p->horizon < 1 || p->horizon > LMPC_MAX_HORIZON) { set_err("horizon out of range [1, 32]"); return LMPC_ERR_INVALID_ARG; }
+  if (!(p->dt > 0) || !(p->mu > 0) || !(p->fz_max > 0) || !(p->mass > 0)) { set_err("dt, mu, fz_max, mass must be > 0"); return LMPC_ERR_INVALID_ARG; }
+  if (p->discretisation != LMPC_DISC_EULER && p->discretisation != LMPC_DISC_ZOH) { set_err("unknown discretisation"); return LMPC_ERR_INVALID_ARG; }
+  if (p->cost_scaling != LMPC_COST_REF_HALF && p->cost_scaling != LMPC_COST_NS_TWO) { set_err("unknown cost_scaling"); return LMPC_ERR_INVALID_ARG; }
+  if (p->precision != LMPC_PREC_F64) { set_err("precision: only LMPC_PREC_F64 is implemented in this build"); return LMPC_ERR_INVALID_ARG; }
+  if (p->solver != LMPC_SOLVER_IPM) { set_err("solver: only LMPC_SOLVER_IPM (+ exact active-set polish) is implemented in this build"); return LMPC_ERR_INVALID_ARG; }
+  for (int i = 0; i < 12; ++i) {
+    if (!(p->r[i] > 0)) { set_err("r weights must be > 0 (the condensed Hessian must be positive definite)"); return LMPC_ERR_INVALID_ARG; }
+    if (!(p->q[i] >= 0)) { set_err("q weights must be >= 0"); return LMPC_ERR_INVALID_ARG; }
+  }
+  return LMPC_OK;
+}
+
+static void fill_kparams(const lmpc_params& p, KParams* k) {
+  k->H = p.horizon;
+  k->zoh = p.discretisation == LMPC_DISC_ZOH ? 1 : 0;
+  k->xoff = p.xref_index_offset;
+  k->max_iter = p.max_iter > 0 ? p.max_iter : 40;
+  k->dt = p.dt; k->mu = p.mu; k->fz_max = p.fz_max; k->mass = p.mass; k->gravity = p.gravity;
+  k->cs = p.cost_scaling == LMPC_COST_NS_TWO ? 2.0 : 1.0;
+  k->act_tol = p.active_tol > 0 ? p.active_tol : 1e-6;
+  for (int i = 0; i < 9; ++i) k->inertia[i] = p.inertia[i];
+  for (int i = 0; i < 12; ++i) { k->q[i] = p.q[i]; k->r[i] = p.r[i]; }
+}
+
+extern "C" lmpc_status lmpc_create(const lmpc_params* params, int32_t max_batch, int32_t device,
+                                   lmpc_handle** out) {
+  if (!out) { set_err("out is NULL"); return LMPC_ERR_INVALID_ARG; }
+  *out = nullptr;
+  lmpc_status st = validate_params(params);
+  if (st != LMPC_OK) return st;
+  if (max_batch < 1) { set_err("max_batch must be >= 1"); return LMPC_ERR_INVALID_ARG; }
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) {
+    set_err(std::string("no CUDA device: this engine has no CPU fallback (") + cudaGetErrorString(e) + ")");
+    return LMPC_ERR_NO_DEVICE;
+  }
+  if (device < 0 || device >= ndev) { set_err("device ordinal out of range"); return LMPC_ERR_INVALID_ARG; }
+  CK(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CK(cudaGetDeviceProperties(&prop, device));
+  if (prop.major < 10) {
+    set_err("device is not sm_100-class; liblmpc.so is built for sm_100a only");
+    return LMPC_ERR_NO_DEVICE;
+  }
+  lmpc_handle* h = new lmpc_handle();
+  h->params = *params;
+  fill_kparams(*params, &h->kp);
+  h->device = device;
+  h->max_batch = max_batch;
+  h->num_sms = prop.multiProcessorCount;
+  h->smem_optin = (int)prop.sharedMemPerBlockOptin;
+  CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+  CK(cudaEventCreate(&h->ev0));
+  CK(cudaEventCreate(&h->ev1));
+  CK(h->d_stats.ensure(sizeof(KStats)));
+  CK(h->d_counter.ensure(sizeof(int)));
+  memset(&h->last_stats, 0, sizeof(KStats));
+  *out = h;
+  return LMPC_OK;
+}
+
+extern "C" void lmpc_destroy(lmpc_handle* h) {
+  if (!h) return;
+  cudaSetDevice(h->device);
+  if (h->stream) cudaStreamSynchronize(h->stream);
+  DevBuf* bufs[] = {&h->d_x0, &h->d_rot, &h->d_foot, &h->d_cmd, &h->d_contact, &h->d_q, &h->d_r, &h->d_mu,
+                    &h->d_fz, &h->d_mass, &h->d_inertia, &h->d_grf, &h->d_status, &h->d_iters, &h->d_active,
+                    &h->d_U, &h->d_stats, &h->d_counter, &h->d_ws};
+  for (DevBuf* b : bufs) b->release();
+  if (h->ev0) cudaEventDestroy(h->ev0);
+  if (h->ev1) cudaEventDestroy(h->ev1);
+  if (h->stream) cudaStreamDestroy(h->stream);
+  delete h;
+}
+
+// Launch classify + solve on `s` for device-resident batch `kb`.  Blocks briefly on the 4-byte
+// n_max read-back that sizes the shared-memory plan.
+static lmpc_status launch_solve(lmpc_handle* h, KBatch kb, cudaStream_t s) {
+  const int H = h->kp.H;
+  KStats* dstats = (KStats*)h->d_stats.p;
+  CK(cudaMemsetAsync(dstats, 0, sizeof(KStats), s));
+  CK(cudaMemsetAsync(h->d_counter.p, 0, sizeof(int), s));
+  CK(cudaEventRecord(h->ev0, s));
+  lmpc::classify_kernel<<<(kb.B + 255) / 256, 256, 0, s>>>(kb.contact, H, kb.B, dstats);
+  h->launches++;
+  int n_max = 0;
+  CK(cudaMemcpyAsync(&n_max, &dstats->n_max, sizeof(int), cudaMemcpyDeviceToHost, s));
+  CK(cudaStreamSynchronize(s));
+  int ncap = n_max > 0 ? n_max : 3;
+  // choose where the two packed matrices live
+  lmpc::SmemPlan pl = lmpc::make_plan(H, ncap, true);
+  int in_smem = 1;
+  if (pl.total_bytes > h->smem_optin) {
+    in_smem = 0;
+    pl = lmpc::make_plan(H, ncap, false);
+    if (pl.total_bytes > h->smem_optin) { set_err("shared-memory plan does not fit even with spilled matrices"); return LMPC_ERR_INVALID_ARG; }
+  }
+  auto kern = lmpc::solve_kernel<kThreads>;
+  CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total_bytes));
+  int occ = 0;
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kThreads, pl.total_bytes));
+  if (occ < 1) { set_err("solve kernel does not fit on an SM"); return LMPC_ERR_CUDA; }
+  int grid = h->num_sms * occ;
+  if (grid > kb.B) grid = kb.B;
+  double* gws = nullptr;
+  if (!in_smem) {
+    size_t bytes = (size_t)grid * 2 * lmpc::packed_size(ncap) * sizeof(double);
+    CK(h->d_ws.ensure(bytes));
+    gws = (double*)h->d_ws.p;
+  }
+  kern<<<grid, kThreads, pl.total_bytes, s>>>(h->kp, kb, dstats, ncap, in_smem, gws, (int*)h->d_counter.p);
+  h->launches++;
+  CK(cudaGetLastError());
+  CK(cudaEventRecord(h->ev1, s));
+  return LMPC_OK;
+}
+
+static lmpc_status finish_solve(lmpc_handle* h, cudaStream_t s) {
+  CK(cudaMemcpyAsync(&h->last_stats, h->d_stats.p, sizeof(KStats), cudaMemcpyDeviceToHost, s));
+  CK(cudaStreamSynchronize(s));
+  CK(cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1));
+  if (h->last_stats.not_ok > 0) {
+    set_err(std::to_string((unsigned long long)h->last_stats.not_ok) + " problem(s) did not converge (grf zeroed)");
+    return LMPC_ERR_NOT_CONVERGED;
+  }
+  return LMPC_OK;
+}
+
+static lmpc_status check_io(lmpc_handle* h, int32_t batch, const lmpc_batch_in* in, const lmpc_batch_out* out) {
+  if (!h || !in || !out) { set_err("NULL handle/in/out"); return LMPC_ERR_INVALID_ARG; }
+  if (batch < 1 || batch > h->max_batch) { set_err("batch must be in [1, max_batch]"); return LMPC_ERR_INVALID_ARG; }
+  if (!in->x0 || !in->rot || !in->foot_pos_abs || !in->cmd || !in->contact) { set_err("x0, rot, foot_pos_abs, cmd, contact are required"); return LMPC_ERR_INVALID_ARG; }
+  if (!out->grf) { set_err("out->grf is required"); return LMPC_ERR_INVALID_ARG; }
+  if ((in->on_device != 0) != (out->on_device != 0)) { set_err("in and out must both be host or both be device pointers"); return LMPC_ERR_INVALID_ARG; }
+  return LMPC_OK;
+}
+
+static KBatch device_batch(const lmpc_batch_in* in, const lmpc_batch_out* out, int batch) {
+  KBatch kb;
+  kb.x0 = in->x0; kb.rot = in->rot; kb.foot = in->foot_pos_abs; kb.cmd = in->cmd; kb.contact = in->contact;
+  kb.q = in->q; kb.r = in->r; kb.mu = in->mu; kb.fzmax = in->fz_max; kb.mass = in->mass; kb.inertia = in->inertia;
+  kb.grf = out->grf; kb.status = out->status; kb.iters = out->iters; kb.active = out->active_set; kb.U = out->U;
+  kb.order = nullptr;
+  kb.B = batch;
+  return kb;
+}
+
+extern "C" lmpc_status lmpc_solve_async(lmpc_handle* h, int32_t batch, const lmpc_batch_in* in,
+                                        const lmpc_batch_out* out, void* cuda_stream) {
+  lmpc_status st = check_io(h, batch, in, out);
+  if (st != LMPC_OK) return st;
+  if (!in->on_device) { set_err("lmpc_solve_async needs device pointers"); return LMPC_ERR_INVALID_ARG; }
+  CK(cudaSetDevice(h->device));
+  cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : h->stream;
+  st = launch_solve(h, device_batch(in, out, batch), s);
+  if (st != LMPC_OK) return st;
+  h->pending = true;
+  h->pending_stream = s;
+  return LMPC_OK;
+}
+
+extern "C" lmpc_status lmpc_wait(lmpc_handle* h) {
+  if (!h) { set_err("NULL handle"); return LMPC_ERR_INVALID_ARG; }
+  if (!h->pending) return LMPC_OK;
+  CK(cudaSetDevice(h->device));
+  h->pending = false;
+  return finish_solve(h, h->pending_stream);
+}
+
+extern "C" lmpc_status lmpc_solve(lmpc_handle* h, int32_t batch, const lmpc_batch_in* in,
+                                  const lmpc_batch_out* out) {
+  lmpc_status st = check_io(h, batch, in, out);
+  if (st != LMPC_OK) return st;
+  CK(cudaSetDevice(h->device));
+  cudaStream_t s = h->stream;
+  if (in->on_device) {
+    st = launch_solve(h, device_batch(in, out, batch), s);
+    if (st != LMPC_OK) return st;
+    return finish_solve(h, s);
+  }
+  // host pointers: stage through device buffers owned by the handle
+  const int H = h->kp.H;
+  const size_t B = (size_t)batch;
+  const int W = LMPC_ACTIVE_WORDS(H);
+  struct In { DevBuf* d; const void* src; size_t bytes; } ins[] = {
+      {&h->d_x0, in->x0, B * 12 * 8}, {&h->d_rot, in->rot, B * 9 * 8}, {&h->d_foot, in->foot_pos_abs, B * 12 * 8},
+      {&h->d_cmd, in->cmd, B * 9 * 8}, {&h->d_contact, in->contact, B * 4 * H}, {&h->d_q, in->q, B * 12 * 8},
+      {&h->d_r, in->r, B * 12 * 8}, {&h->d_mu, in->mu, B * 8}, {&h->d_fz, in->fz_max, B * 8},
+      {&h->d_mass, in->mass, B * 8}, {&h->d_inertia, in->inertia, B * 9 * 8}};
+  for (auto& i : ins) {
+    if (!i.src) continue;
+    CK(i.d->ensure(i.bytes));
+    CK(cudaMemcpyAsync(i.d->p, i.src, i.bytes, cudaMemcpyHostToDevice, s));
+  }
+  CK(h->d_grf.ensure(B * 12 * 8));
+  if (out->status) CK(h->d_status.ensure(B * 4));
+  if (out->iters) CK(h->d_iters.ensure(B * 4));
+  if (out->active_set) CK(h->d_active.ensure(B * W * 4));
+  if (out->U) CK(h->d_U.ensure(B * 12 * H * 8));
+  KBatch kb;
+  kb.x0 = (const double*)h->d_x0.p; kb.rot = (const double*)h->d_rot.p; kb.foot = (const double*)h->d_foot.p;
+  kb.cmd = (const double*)h->d_cmd.p; kb.contact = (const uint8_t*)h->d_contact.p;
+  kb.q = in->q ? (const double*)h->d_q.p : nullptr; kb.r = in->r ? (const double*)h->d_r.p : nullptr;
+  kb.mu = in->mu ? (const double*)h->d_mu.p : nullptr; kb.fzmax = in->fz_max ? (const double*)h->d_fz.p : nullptr;
+  kb.mass = in->mass ? (const double*)h->d_mass.p : nullptr; kb.inertia = in->inertia ? (const double*)h->d_inertia.p : nullptr;
+  kb.grf = (double*)h->d_grf.p; kb.status = out->status ? (int*)h->d_status.p : nullptr;
+  kb.iters = out->iters ? (int*)h->d_iters.p : nullptr; kb.active = out->active_set ? (uint32_t*)h->d_active.p : nullptr;
+  kb.U = out->U ? (double*)h->d_U.p : nullptr; kb.order = nullptr; kb.B = batch;
+  st = launch_solve(h, kb, s);
+  if (st != LMPC_OK) return st;
+  CK(cudaMemcpyAsync(out->grf, kb.grf, B * 12 * 8, cudaMemcpyDeviceToHost, s));
+  if (out->status) CK(cudaMemcpyAsync(out->status, kb.status, B * 4, cudaMemcpyDeviceToHost, s));
+  if (out->iters) CK(cudaMemcpyAsync(out->iters, kb.iters, B * 4, cudaMemcpyDeviceToHost, s));
+  if (out->active_set) CK(cudaMemcpyAsync(out->active_set, kb.active, B * W * 4, cudaMemcpyDeviceToHost, s));
+  if (out->U) CK(cudaMemcpyAsync(out->U, kb.U, B * 12 * H * 8, cudaMemcpyDeviceToHost, s));
+  return finish_solve(h, s);
+}
+
+extern "C" lmpc_status lmpc_reset_warm_start(lmpc_handle* h) {
+  if (!h) { set_err("NULL handle"); return LMPC_ERR_INVALID_ARG; }
+  return LMPC_OK;  // every solve of this build is a cold start; nothing is cached on the device
+}
+
+extern "C" int64_t lmpc_launch_count(const lmpc_handle* h) { return h ? h->launches : 0; }
+extern "C" float lmpc_last_kernel_ms(const lmpc_handle* h) { return h ? h->last_ms : 0.f; }
+
+extern "C" lmpc_status lmpc_last_stats(const lmpc_handle* h, double* mean_n_eff, double* mean_fact,
+                                       double* flops_executed) {
+  if (!h) { set_err("NULL handle"); return LMPC_ERR_INVALID_ARG; }
+  const double np = h->last_stats.problems > 0 ? (double)h->last_stats.problems : 1.0;
+  if (mean_n_eff) *mean_n_eff = (double)h->last_stats.sum_n / np;
+  if (mean_fact) *mean_fact = (double)h->last_stats.sum_fact / np;
+  if (flops_executed) *flops_executed = h->last_stats.flops;
+  return LMPC_OK;
+}
