@@ -9,24 +9,76 @@
 
 #include "../../include/lmpc.h"
 #include "lmpc_solver.cuh"
+#include "lmpc_warp_solve.cuh"
 
 namespace lmpc {
 
 // ---------------------------------------------------------------- kernels
 
-// Reduced dimension of every problem (3 per stance leg-step) and the batch maximum: sizes the
-// shared-memory plan of the solve launch.
+// Reduced dimension of every problem (3 per stance leg-step) -> size class.  Class A (n <= 63:
+// the one-warp-per-QP path) and class B (everything larger: the CTA-per-QP path) are compacted
+// into two index lists with warp-aggregated atomics; n_max of class B sizes its shared memory.
+// counts[0] = |A|, counts[1] = |B|.
 __global__ void classify_kernel(const uint8_t* __restrict__ contact, int H, int B,
-                                KStats* __restrict__ stats) {
-  int i = blockIdx.x * blockDim.x + threadIdx.x;
-  int n = 0;
+                                KStats* __restrict__ stats, int* __restrict__ orderA,
+                                int* __restrict__ orderB, int* __restrict__ counts) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int lane = threadIdx.x & 31;
+  int n = -1;
   if (i < B) {
     const uint8_t* c = contact + (size_t)(4 * H) * i;
+    n = 0;
     for (int t = 0; t < 4 * H; ++t) n += c[t] ? 3 : 0;
   }
+  const bool isA = n >= 0 && n <= 3 * WNBMAX;
+  const bool isB = n > 3 * WNBMAX;
+  const unsigned mA = __ballot_sync(0xffffffffu, isA), mB = __ballot_sync(0xffffffffu, isB);
+  int baseA = 0, baseB = 0;
+  if (lane == 0) {
+    if (mA) baseA = atomicAdd(&counts[0], __popc(mA));
+    if (mB) baseB = atomicAdd(&counts[1], __popc(mB));
+  }
+  baseA = __shfl_sync(0xffffffffu, baseA, 0);
+  baseB = __shfl_sync(0xffffffffu, baseB, 0);
+  const unsigned lt = (1u << lane) - 1u;
+  if (isA) orderA[baseA + __popc(mA & lt)] = i;
+  if (isB) orderB[baseB + __popc(mB & lt)] = i;
+  int nB = isB ? n : 0;
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) n = max(n, __shfl_xor_sync(0xffffffffu, n, o));
-  if ((threadIdx.x & 31) == 0 && n > 0) atomicMax(&stats->n_max, n);
+  for (int o = 16; o > 0; o >>= 1) nB = max(nB, __shfl_xor_sync(0xffffffffu, nB, o));
+  if (lane == 0 && nB > 0) atomicMax(&stats->n_max, nB);
+}
+
+// Persistent one-warp-per-QP solve (class A).  One warp per CTA: no block barrier exists in this
+// kernel.  Problems are handed out by an atomic counter; the scaled Hessian of the problem in
+// flight lives in this CTA's 32 KB slot of the L2-resident workspace `gws`.
+__global__ void __launch_bounds__(32) solve_warp_kernel(const __grid_constant__ KParams P,
+                                                        const __grid_constant__ KBatch Bt,
+                                                        KStats* stats, double* gws,
+                                                        const int* __restrict__ count,
+                                                        int* work_counter) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const WarpPlan pl = make_warp_plan(P.H);
+  double* Hg = gws + (size_t)blockIdx.x * (WN * WN);
+  const int lane = threadIdx.x;
+  const int total = *count;
+  WarpStats ws;
+  for (;;) {
+    int w = 0;
+    if (lane == 0) w = atomicAdd(work_counter, 1);
+    w = __shfl_sync(0xffffffffu, w, 0);
+    if (w >= total) break;
+    solve_one_warp(P, Bt, ws, pl, smem, Hg, Bt.order[w]);
+  }
+  if (lane == 0 && ws.problems) {
+    atomicAdd(&stats->problems, ws.problems);
+    atomicAdd(&stats->sum_n, ws.sum_n);
+    atomicAdd(&stats->sum_fact, ws.sum_fact);
+    atomicAdd(&stats->sum_polish, ws.sum_polish);
+    if (ws.not_ok) atomicAdd(&stats->not_ok, ws.not_ok);
+    if (ws.ipm_only) atomicAdd(&stats->ipm_only, ws.ipm_only);
+    atomicAdd(&stats->flops, ws.flops);
+  }
 }
 
 // Persistent solve: one CTA per QP at a time, problems handed out by an atomic counter.
@@ -34,7 +86,8 @@ template <int NT>
 __global__ void __launch_bounds__(NT) solve_kernel(const __grid_constant__ KParams P,
                                                    const __grid_constant__ KBatch Bt,
                                                    KStats* stats, int ncap, int mats_in_smem,
-                                                   double* gws, int* work_counter) {
+                                                   double* gws, const int* __restrict__ count,
+                                                   int* work_counter) {
   extern __shared__ __align__(16) unsigned char smem[];
   const SmemPlan pl = make_plan(P.H, ncap, mats_in_smem != 0);
   double* gH = nullptr;
@@ -50,8 +103,8 @@ __global__ void __launch_bounds__(NT) solve_kernel(const __grid_constant__ KPara
     __syncthreads();
     const int w = si[INT_WORK];
     __syncthreads();
-    if (w >= Bt.B) break;
-    const int pi = Bt.order ? Bt.order[w] : w;
+    if (w >= *count) break;
+    const int pi = Bt.order[w];
     solve_one<NT>(P, Bt, stats, pl, smem, gH, gM, pi);
   }
 }
@@ -106,7 +159,9 @@ struct lmpc_handle {
   // device staging for host-pointer calls
   DevBuf d_x0, d_rot, d_foot, d_cmd, d_contact, d_q, d_r, d_mu, d_fz, d_mass, d_inertia;
   DevBuf d_grf, d_status, d_iters, d_active, d_U;
-  DevBuf d_stats, d_counter, d_ws;
+  DevBuf d_stats, d_counter, d_ws, d_wsA, d_order;
+  cudaEvent_t ev_cls = nullptr;
+  int* h_cls = nullptr;  // pinned: n_max, |A|, |B|
   KStats last_stats;
   float last_ms = 0.f;
   int64_t launches = 0;
@@ -172,8 +227,11 @@ extern "C" lmpc_status lmpc_create(const lmpc_params* params, int32_t max_batch,
   CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
   CK(cudaEventCreate(&h->ev0));
   CK(cudaEventCreate(&h->ev1));
+  CK(cudaEventCreateWithFlags(&h->ev_cls, cudaEventDisableTiming));
+  CK(cudaMallocHost((void**)&h->h_cls, 4 * sizeof(int)));
   CK(h->d_stats.ensure(sizeof(KStats)));
-  CK(h->d_counter.ensure(sizeof(int)));
+  CK(h->d_counter.ensure(4 * sizeof(int)));  // work counters A, B ; counts A, B
+  CK(h->d_order.ensure(2 * (size_t)max_batch * sizeof(int)));
   memset(&h->last_stats, 0, sizeof(KStats));
   *out = h;
   return LMPC_OK;
@@ -185,52 +243,81 @@ extern "C" void lmpc_destroy(lmpc_handle* h) {
   if (h->stream) cudaStreamSynchronize(h->stream);
   DevBuf* bufs[] = {&h->d_x0, &h->d_rot, &h->d_foot, &h->d_cmd, &h->d_contact, &h->d_q, &h->d_r, &h->d_mu,
                     &h->d_fz, &h->d_mass, &h->d_inertia, &h->d_grf, &h->d_status, &h->d_iters, &h->d_active,
-                    &h->d_U, &h->d_stats, &h->d_counter, &h->d_ws};
+                    &h->d_U, &h->d_stats, &h->d_counter, &h->d_ws, &h->d_wsA, &h->d_order};
   for (DevBuf* b : bufs) b->release();
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
+  if (h->ev_cls) cudaEventDestroy(h->ev_cls);
+  if (h->h_cls) cudaFreeHost(h->h_cls);
   if (h->stream) cudaStreamDestroy(h->stream);
   delete h;
 }
 
-// Launch classify + solve on `s` for device-resident batch `kb`.  Blocks briefly on the 4-byte
-// n_max read-back that sizes the shared-memory plan.
+// Launch classify + the two size-class solves on `s` for the device-resident batch `kb`.
+// The class-A (one warp per QP) kernel is enqueued right behind the classification; the host
+// only waits for the 12-byte read-back that sizes the class-B launch, while class A runs.
 static lmpc_status launch_solve(lmpc_handle* h, KBatch kb, cudaStream_t s) {
   const int H = h->kp.H;
   KStats* dstats = (KStats*)h->d_stats.p;
+  int* ctr = (int*)h->d_counter.p;       // [0] work A, [1] work B, [2] |A|, [3] |B|
+  int* orderA = (int*)h->d_order.p;
+  int* orderB = orderA + h->max_batch;
   CK(cudaMemsetAsync(dstats, 0, sizeof(KStats), s));
-  CK(cudaMemsetAsync(h->d_counter.p, 0, sizeof(int), s));
+  CK(cudaMemsetAsync(ctr, 0, 4 * sizeof(int), s));
   CK(cudaEventRecord(h->ev0, s));
-  lmpc::classify_kernel<<<(kb.B + 255) / 256, 256, 0, s>>>(kb.contact, H, kb.B, dstats);
+  lmpc::classify_kernel<<<(kb.B + 255) / 256, 256, 0, s>>>(kb.contact, H, kb.B, dstats, orderA, orderB, ctr + 2);
   h->launches++;
-  int n_max = 0;
-  CK(cudaMemcpyAsync(&n_max, &dstats->n_max, sizeof(int), cudaMemcpyDeviceToHost, s));
-  CK(cudaStreamSynchronize(s));
-  int ncap = n_max > 0 ? n_max : 3;
-  // choose where the two packed matrices live
-  lmpc::SmemPlan pl = lmpc::make_plan(H, ncap, true);
-  int in_smem = 1;
-  if (pl.total_bytes > h->smem_optin) {
-    in_smem = 0;
-    pl = lmpc::make_plan(H, ncap, false);
-    if (pl.total_bytes > h->smem_optin) { set_err("shared-memory plan does not fit even with spilled matrices"); return LMPC_ERR_INVALID_ARG; }
+  CK(cudaMemcpyAsync(h->h_cls, &dstats->n_max, sizeof(int), cudaMemcpyDeviceToHost, s));
+  CK(cudaMemcpyAsync(h->h_cls + 1, ctr + 2, 2 * sizeof(int), cudaMemcpyDeviceToHost, s));
+  CK(cudaEventRecord(h->ev_cls, s));
+  // ---- class A: one warp per QP
+  {
+    const lmpc::WarpPlan wp = lmpc::make_warp_plan(H);
+    auto kernA = lmpc::solve_warp_kernel;
+    CK(cudaFuncSetAttribute(kernA, cudaFuncAttributeMaxDynamicSharedMemorySize, wp.total_bytes));
+    int occ = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernA, 32, wp.total_bytes));
+    if (occ < 1) { set_err("warp solve kernel does not fit on an SM"); return LMPC_ERR_CUDA; }
+    int grid = h->num_sms * occ;
+    if (grid > kb.B) grid = kb.B;
+    CK(h->d_wsA.ensure((size_t)grid * lmpc::WN * lmpc::WN * sizeof(double)));
+    KBatch ka = kb;
+    ka.order = orderA;
+    kernA<<<grid, 32, wp.total_bytes, s>>>(h->kp, ka, dstats, (double*)h->d_wsA.p, ctr + 2, ctr + 0);
+    h->launches++;
+    CK(cudaGetLastError());
   }
-  auto kern = lmpc::solve_kernel<kThreads>;
-  CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total_bytes));
-  int occ = 0;
-  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kThreads, pl.total_bytes));
-  if (occ < 1) { set_err("solve kernel does not fit on an SM"); return LMPC_ERR_CUDA; }
-  int grid = h->num_sms * occ;
-  if (grid > kb.B) grid = kb.B;
-  double* gws = nullptr;
-  if (!in_smem) {
-    size_t bytes = (size_t)grid * 2 * lmpc::packed_size(ncap) * sizeof(double);
-    CK(h->d_ws.ensure(bytes));
-    gws = (double*)h->d_ws.p;
+  CK(cudaEventSynchronize(h->ev_cls));
+  const int n_max = h->h_cls[0], countB = h->h_cls[2];
+  if (countB > 0) {
+    // ---- class B: one CTA per QP; choose where the two packed matrices live
+    int ncap = n_max > 0 ? n_max : 3;
+    lmpc::SmemPlan pl = lmpc::make_plan(H, ncap, true);
+    int in_smem = 1;
+    if (pl.total_bytes > h->smem_optin) {
+      in_smem = 0;
+      pl = lmpc::make_plan(H, ncap, false);
+      if (pl.total_bytes > h->smem_optin) { set_err("shared-memory plan does not fit even with spilled matrices"); return LMPC_ERR_INVALID_ARG; }
+    }
+    auto kern = lmpc::solve_kernel<kThreads>;
+    CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total_bytes));
+    int occ = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kThreads, pl.total_bytes));
+    if (occ < 1) { set_err("solve kernel does not fit on an SM"); return LMPC_ERR_CUDA; }
+    int grid = h->num_sms * occ;
+    if (grid > countB) grid = countB;
+    double* gws = nullptr;
+    if (!in_smem) {
+      size_t bytes = (size_t)grid * 2 * lmpc::packed_size(ncap) * sizeof(double);
+      CK(h->d_ws.ensure(bytes));
+      gws = (double*)h->d_ws.p;
+    }
+    KBatch kbB = kb;
+    kbB.order = orderB;
+    kern<<<grid, kThreads, pl.total_bytes, s>>>(h->kp, kbB, dstats, ncap, in_smem, gws, ctr + 3, ctr + 1);
+    h->launches++;
+    CK(cudaGetLastError());
   }
-  kern<<<grid, kThreads, pl.total_bytes, s>>>(h->kp, kb, dstats, ncap, in_smem, gws, (int*)h->d_counter.p);
-  h->launches++;
-  CK(cudaGetLastError());
   CK(cudaEventRecord(h->ev1, s));
   return LMPC_OK;
 }

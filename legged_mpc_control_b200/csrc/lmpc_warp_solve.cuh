@@ -1,0 +1,635 @@
+// lmpc_warp_solve.cuh — one-warp-per-QP driver (n <= 64): same algorithm and formulas as
+// solve_one() in lmpc_solver.cuh (SRBD build -> discretise -> structured condense -> Mehrotra
+// interior point -> exact active-set polish), re-mapped onto a single warp with the dense
+// kernels of lmpc_warp.cuh.  Reference citations as in lmpc_solver.cuh.
+#pragma once
+#include "lmpc_solver.cuh"
+#include "lmpc_warp.cuh"
+
+namespace lmpc {
+
+struct WarpStats {
+  unsigned long long problems = 0, sum_n = 0, sum_fact = 0, sum_polish = 0, not_ok = 0, ipm_only = 0;
+  double flops = 0;
+};
+
+// 3x3 block (b1 >= b2 in block order, hence j1 >= j2) of cs*(B_qp' Qbar B_qp + Rbar), unscaled
+// by the cost normalisation.  out[a1 + 3*a2].
+__device__ __forceinline__ void wblock(int H, double dt2, double theta, double cs, double im2,
+                                       const double* __restrict__ qw, const double* __restrict__ rw,
+                                       const double* __restrict__ Bw, const double* __restrict__ cosv,
+                                       const double* __restrict__ sinv, const double* __restrict__ Cs,
+                                       const double* __restrict__ Ss, int j1, int l1, int j2, int l2,
+                                       bool same, double* out) {
+  double n00 = 0, n01 = 0, n10 = 0, n11 = 0, n22 = 0;
+  const double o1c = theta * cosv[j1] - Cs[j1], o1s = theta * sinv[j1] - Ss[j1];
+  const double o2c = theta * cosv[j2] - Cs[j2], o2s = theta * sinv[j2] - Ss[j2];
+  for (int k = j1; k < H; ++k) {
+    const double a1 = dt2 * (Cs[k] + o1c), bb1 = dt2 * (Ss[k] + o1s);
+    const double a2 = dt2 * (Cs[k] + o2c), bb2 = dt2 * (Ss[k] + o2s);
+    const double g1 = dt2 * ((double)(k - j1) + theta), g2 = dt2 * ((double)(k - j2) + theta);
+    n00 += a1 * qw[0] * a2 + bb1 * qw[1] * bb2;
+    n01 += a1 * qw[0] * bb2 - bb1 * qw[1] * a2;
+    n10 += bb1 * qw[0] * a2 - a1 * qw[1] * bb2;
+    n11 += bb1 * qw[0] * bb2 + a1 * qw[1] * a2;
+    n22 += g1 * g2;
+  }
+  const double cnt = (double)(H - j1) * dt2;
+  const double m00 = n00 + cnt * qw[6], m11 = n11 + cnt * qw[7], m22 = n22 * qw[2] + cnt * qw[8];
+  double t[9];
+#pragma unroll
+  for (int a2 = 0; a2 < 3; ++a2) {
+    const double* bc = Bw + 3 * (3 * l2 + a2);
+    t[0 + 3 * a2] = m00 * bc[0] + n01 * bc[1];
+    t[1 + 3 * a2] = n10 * bc[0] + m11 * bc[1];
+    t[2 + 3 * a2] = m22 * bc[2];
+  }
+#pragma unroll
+  for (int a1 = 0; a1 < 3; ++a1) {
+    const double* br = Bw + 3 * (3 * l1 + a1);
+#pragma unroll
+    for (int a2 = 0; a2 < 3; ++a2) {
+      double v = br[0] * t[0 + 3 * a2] + br[1] * t[1 + 3 * a2] + br[2] * t[2 + 3 * a2];
+      if (a1 == a2) {
+        v += (n22 * qw[3 + a1] + cnt * qw[9 + a1]) * im2;
+        if (same) v += rw[3 * l1 + a1];
+      }
+      out[a1 + 3 * a2] = cs * v;
+    }
+  }
+}
+
+__device__ __forceinline__ void pair_from_index(int pr, int& b1, int& b2) {
+  b1 = (int)((sqrt(8.0 * (double)pr + 1.0) - 1.0) * 0.5);
+  while (((b1 + 1) * (b1 + 2)) / 2 <= pr) ++b1;
+  while ((b1 * (b1 + 1)) / 2 > pr) --b1;
+  b2 = pr - (b1 * (b1 + 1)) / 2;
+}
+
+__device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws, const WarpPlan& pl,
+                               unsigned char* smem, double* Hg, int pi) {
+  const int lane = threadIdx.x & 31;
+  const int H = P.H;
+  double* sd = reinterpret_cast<double*>(smem);
+  double* Lp = sd + pl.oLP;
+  double* u = sd + pl.oU;
+  double* gs = sd + pl.oGS;
+  double* z = sd + pl.oZ;
+  double* prm = sd + pl.oPRM;
+  double* t8 = sd + pl.oT8;
+  double* hu = sd + pl.oHU;
+  double* rd = sd + pl.oRD;
+  double* dua = sd + pl.oDUA;
+  double* du = sd + pl.oDU;
+  double* wrow = sd + pl.oWROW;
+  double* Bw = sd + pl.oBW;
+  double* cosv = sd + pl.oCOS;
+  double* sinv = sd + pl.oSIN;
+  double* Cs = sd + pl.oCS;
+  double* Ss = sd + pl.oSS;
+  double* e = sd + pl.oE;
+  double* aj = sd + pl.oAJ;
+  double* bj = sd + pl.oBJ;
+  unsigned char* blk = smem + pl.oBLK;
+  signed char* face = reinterpret_cast<signed char*>(smem + pl.oFACE);
+  short* bmap = reinterpret_cast<short*>(smem + pl.oBMAP);
+
+  const double dt = P.dt, dt2 = P.dt * P.dt, theta = P.zoh ? 0.5 : 0.0;
+  const size_t p64 = (size_t)pi;
+  const double* x0 = Bt.x0 + 12 * p64;
+  const double* rot = Bt.rot + 9 * p64;
+  const double* foot = Bt.foot + 12 * p64;
+  const double* cmd = Bt.cmd + 9 * p64;
+  const uint8_t* contact = Bt.contact + (size_t)(4 * H) * p64;
+
+  __syncwarp();
+  // ---------------- stage 1: parameters, SRBD build, yaw references, stance-block list
+  if (lane < 12) {
+    prm[PRM_Q + lane] = Bt.q ? Bt.q[12 * p64 + lane] : P.q[lane];
+    prm[PRM_R + lane] = Bt.r ? Bt.r[12 * p64 + lane] : P.r[lane];
+  }
+  if (lane == 0) {
+    prm[PRM_MU] = Bt.mu ? Bt.mu[p64] : P.mu;
+    prm[PRM_FZ] = Bt.fzmax ? Bt.fzmax[p64] : P.fz_max;
+    prm[PRM_MASS] = Bt.mass ? Bt.mass[p64] : P.mass;
+    double R[9], I[9], RI[9], Iw[9];
+    for (int k = 0; k < 9; ++k) { R[k] = rot[k]; I[k] = Bt.inertia ? Bt.inertia[9 * p64 + k] : P.inertia[k]; }
+    for (int c = 0; c < 3; ++c)
+      for (int r = 0; r < 3; ++r)
+        RI[r + 3 * c] = R[r] * I[3 * c] + R[r + 3] * I[1 + 3 * c] + R[r + 6] * I[2 + 3 * c];
+    for (int c = 0; c < 3; ++c)
+      for (int r = 0; r < 3; ++r)
+        Iw[r + 3 * c] = RI[r] * R[c] + RI[r + 3] * R[c + 3] + RI[r + 6] * R[c + 6];
+    const double a = Iw[0], b = Iw[3], c = Iw[6], d = Iw[1], ee = Iw[4], f = Iw[7], g = Iw[2], h = Iw[5], i = Iw[8];
+    const double c00 = ee * i - f * h, c01 = -(d * i - f * g), c02 = d * h - ee * g;
+    const double c10 = -(b * i - c * h), c11 = a * i - c * g, c12 = -(a * h - b * g);
+    const double c20 = b * f - c * ee, c21 = -(a * f - c * d), c22 = a * ee - b * d;
+    const double id = 1.0 / (a * c00 + b * c01 + c * c02);
+    double Ii[9];
+    Ii[0] = c00 * id; Ii[3] = c10 * id; Ii[6] = c20 * id;
+    Ii[1] = c01 * id; Ii[4] = c11 * id; Ii[7] = c21 * id;
+    Ii[2] = c02 * id; Ii[5] = c12 * id; Ii[8] = c22 * id;
+    for (int leg = 0; leg < 4; ++leg) {
+      const double rx = foot[3 * leg], ry = foot[3 * leg + 1], rz = foot[3 * leg + 2];
+      for (int s = 0; s < 3; ++s) {
+        Bw[s + 3 * (3 * leg + 0)] = Ii[s + 3] * rz - Ii[s + 6] * ry;
+        Bw[s + 3 * (3 * leg + 1)] = -Ii[s] * rz + Ii[s + 6] * rx;
+        Bw[s + 3 * (3 * leg + 2)] = Ii[s] * ry - Ii[s + 3] * rx;
+      }
+    }
+    for (int r = 0; r < 3; ++r) prm[PRM_VW + r] = R[r] * cmd[3] + R[r + 3] * cmd[4] + R[r + 6] * cmd[5];
+  }
+  int nb = 0;
+  for (int base = 0; base < 4 * H; base += 32) {  // stance-block list by ballot + prefix popcount
+    const int idx = base + lane;
+    const bool fl = idx < 4 * H && contact[idx] != 0;
+    const unsigned m = __ballot_sync(0xffffffffu, fl);
+    const int pos = nb + __popc(m & ((1u << lane) - 1u));
+    if (idx < 4 * H) bmap[idx] = fl ? (short)pos : (short)-1;
+    if (fl && pos < WNBMAX) { blk[2 * pos] = (unsigned char)(idx >> 2); blk[2 * pos + 1] = (unsigned char)(idx & 3); }
+    nb += __popc(m);
+  }
+  for (int k = lane; k < H; k += 32) {
+    const double yawk = x0[2] + cmd[8] * dt * (double)(k + P.xoff);
+    double sv, cv;
+    sincos(yawk, &sv, &cv);
+    cosv[k] = cv; sinv[k] = sv;
+  }
+  __syncwarp();
+  const int n = 3 * nb;
+  const double mu = prm[PRM_MU], fzm = prm[PRM_FZ], mass = prm[PRM_MASS];
+  const double* qw = prm + PRM_Q;
+  const double* rw = prm + PRM_R;
+
+  if (lane == 0) {  // free response and prefix sums (serial, H steps)
+    double th0 = x0[0], th1 = x0[1], th2 = x0[2], p0 = x0[3], p1 = x0[4], p2 = x0[5];
+    const double w0 = x0[6], w1 = x0[7], w2 = x0[8], v0 = x0[9], v1 = x0[10];
+    double v2 = x0[11];
+    double ac = 0, as = 0;
+    for (int k = 0; k < H; ++k) {
+      const double c = cosv[k], s = sinv[k];
+      ac += c; as += s; Cs[k] = ac; Ss[k] = as;
+      th0 += dt * (c * w0 + s * w1);
+      th1 += dt * (-s * w0 + c * w1);
+      th2 += dt * w2;
+      p0 += dt * v0; p1 += dt * v1;
+      p2 += dt * v2 - theta * dt2 * P.gravity;
+      v2 -= P.gravity * dt;
+      const double t = dt * (double)(k + P.xoff);
+      double* ek = e + 12 * k;
+      ek[0] = th0 - cmd[0]; ek[1] = th1 - cmd[1]; ek[2] = th2 - (x0[2] + cmd[8] * t);
+      ek[3] = p0 - (x0[3] + prm[PRM_VW] * t); ek[4] = p1 - (x0[4] + prm[PRM_VW + 1] * t); ek[5] = p2 - cmd[2];
+      ek[6] = w0 - cmd[6]; ek[7] = w1 - cmd[7]; ek[8] = w2 - cmd[8];
+      ek[9] = v0 - prm[PRM_VW]; ek[10] = v1 - prm[PRM_VW + 1]; ek[11] = v2;
+    }
+  }
+  __syncwarp();
+  for (int j = lane; j < H; j += 32) {
+    double a0 = 0, a1 = 0, a2 = 0, b0 = 0, b1 = 0, b2 = 0, sw0 = 0, sw1 = 0, sw2 = 0, sv0 = 0, sv1 = 0, sv2 = 0;
+    for (int k = j; k < H; ++k) {
+      const double ea = dt2 * (Cs[k] - Cs[j] + theta * cosv[j]);
+      const double eb = dt2 * (Ss[k] - Ss[j] + theta * sinv[j]);
+      const double gam = dt2 * ((double)(k - j) + theta);
+      const double* ek = e + 12 * k;
+      const double w0 = qw[0] * ek[0], w1 = qw[1] * ek[1], w2 = qw[2] * ek[2];
+      a0 += ea * w0 - eb * w1;
+      a1 += eb * w0 + ea * w1;
+      a2 += gam * w2;
+      b0 += gam * qw[3] * ek[3]; b1 += gam * qw[4] * ek[4]; b2 += gam * qw[5] * ek[5];
+      sw0 += ek[6]; sw1 += ek[7]; sw2 += ek[8];
+      sv0 += ek[9]; sv1 += ek[10]; sv2 += ek[11];
+    }
+    aj[3 * j + 0] = a0 + dt * qw[6] * sw0; aj[3 * j + 1] = a1 + dt * qw[7] * sw1; aj[3 * j + 2] = a2 + dt * qw[8] * sw2;
+    bj[3 * j + 0] = b0 + dt * qw[9] * sv0; bj[3 * j + 1] = b1 + dt * qw[10] * sv1; bj[3 * j + 2] = b2 + dt * qw[11] * sv2;
+  }
+  __syncwarp();
+
+  const int W = (24 * H + 31) / 32;
+  if (n == 0) {
+    if (lane == 0) {
+      if (Bt.status) Bt.status[p64] = 0;
+      if (Bt.iters) Bt.iters[p64] = 0;
+    }
+    if (lane < 12) Bt.grf[12 * p64 + lane] = 0.0;
+    if (Bt.U) for (int i = lane; i < 12 * H; i += 32) Bt.U[(size_t)(12 * H) * p64 + i] = 0.0;
+    if (Bt.active)
+      for (int w = lane; w < W; w += 32) {
+        const int lo = 32 * w, hi = min(32 * w + 32, 24 * H);
+        Bt.active[(size_t)W * p64 + w] = (hi - lo == 32) ? 0xffffffffu : ((1u << (hi - lo)) - 1u);
+      }
+    ws.problems++;
+    __syncwarp();
+    return;
+  }
+
+  // ---------------- stage 3: reduced Hessian into the L2 workspace (full symmetric 64x64)
+  const double im2 = 1.0 / (mass * mass);
+  double sc;
+  {
+    double dmax = 0;
+    if (lane < nb) {
+      double o[9];
+      const int j = blk[2 * lane], l = blk[2 * lane + 1];
+      wblock(H, dt2, theta, P.cs, im2, qw, rw, Bw, cosv, sinv, Cs, Ss, j, l, j, l, true, o);
+      dmax = fmax(fabs(o[0]), fmax(fabs(o[4]), fabs(o[8])));
+    }
+    dmax = wmax(dmax);
+    sc = 1.0 / dmax;
+    // identity padding for rows/cols >= n
+    for (int idx = lane; idx < WN * (WN - n); idx += 32) {
+      const int c = n + idx / WN, r = idx % WN;
+      __stcg(Hg + c * WN + r, (r == c) ? 1.0 : 0.0);
+      __stcg(Hg + r * WN + c, (r == c) ? 1.0 : 0.0);
+    }
+    const int npairs = (nb * (nb + 1)) >> 1;
+    for (int pr = lane; pr < npairs; pr += 32) {
+      int b1, b2;
+      pair_from_index(pr, b1, b2);
+      double o[9];
+      wblock(H, dt2, theta, P.cs, im2, qw, rw, Bw, cosv, sinv, Cs, Ss, blk[2 * b1], blk[2 * b1 + 1], blk[2 * b2],
+             blk[2 * b2 + 1], b1 == b2, o);
+#pragma unroll
+      for (int a1 = 0; a1 < 3; ++a1)
+#pragma unroll
+        for (int a2 = 0; a2 < 3; ++a2) {
+          const int r = 3 * b1 + a1, c = 3 * b2 + a2;
+          const double v = sc * o[a1 + 3 * a2];
+          __stcg(Hg + c * WN + r, v);
+          __stcg(Hg + r * WN + c, v);  // (diagonal blocks are symmetric, so the double write agrees)
+        }
+    }
+    if (lane < nb) {
+      const int j = blk[2 * lane], l = blk[2 * lane + 1];
+#pragma unroll
+      for (int a = 0; a < 3; ++a) {
+        const double* bc = Bw + 3 * (3 * l + a);
+        gs[3 * lane + a] = sc * P.cs * (bc[0] * aj[3 * j] + bc[1] * aj[3 * j + 1] + bc[2] * aj[3 * j + 2] + bj[3 * j + a] / mass);
+      }
+    }
+    for (int i = n + lane; i < WN; i += 32) gs[i] = 0.0;
+  }
+  __threadfence_block();
+  __syncwarp();  // Hg visible to every lane; setup scratch (aliased with hu/rd/dua/du/wrow) is dead from here on
+  double gsinf = wmax(fmax(fabs(gs[lane]), fabs(gs[lane + 32])));
+  const double rd_tol = 1e-9 * (gsinf > 1.0 ? gsinf : 1.0);
+  const double dual_tol = 1e-9 * (gsinf > sc ? gsinf : sc);
+  const double feas_tol = 1e-9;
+  const int m = 5 * nb;
+
+  // ---------------- stage 4a: interior point (feasible start)
+  u[lane] = 0.0; u[lane + 32] = 0.0;
+  __syncwarp();
+  if (lane < nb) u[3 * lane + 2] = 0.5 * fzm;
+  for (int i = lane; i < 3 * WN; i += 32) wrow[i] = 0.0;
+  __syncwarp();
+  {
+    double y0, y1;
+    wsymv(Hg, u, lane, y0, y1);
+    double ginf = wmax(fmax(fabs(y0 + gs[lane]), fabs(y1 + gs[lane + 32])));
+    double ssum = 0;
+    double s[5];
+    if (lane < nb) {
+      blk_slack(u + 3 * lane, mu, fzm, s);
+      ssum = s[0] + s[1] + s[2] + s[3] + s[4];
+    }
+    ssum = wsum(ssum);
+    const double zc = (ginf > 1e-6 ? ginf : 1e-6) * (ssum / (double)m);
+    if (lane < nb)
+      for (int r = 0; r < 5; ++r) z[5 * lane + r] = zc / s[r];
+  }
+  __syncwarp();
+
+  int n_ipm = 0, n_polish = 0, status = -1;
+  const int max_iter = P.max_iter;
+  bool solved = false;
+  for (int stage = 0; stage < 3 && !solved; ++stage) {
+    const double mu_tol = stage == 0 ? 1e-7 : (stage == 1 ? 1e-10 : 1e-13);
+    bool ipm_converged = false, ipm_broken = false;
+    while (n_ipm < max_iter) {
+      double h0, h1;
+      wsymv(Hg, u, lane, h0, h1);
+      hu[lane] = h0; hu[lane + 32] = h1;
+      rd[lane] = 0.0; rd[lane + 32] = 0.0;
+      __syncwarp();
+      double rdinf = 0, sz = 0;
+      if (lane < nb) {
+        const int b = lane;
+        double s[5], ct[3];
+        blk_slack(u + 3 * b, mu, fzm, s);
+        const double* zb = z + 5 * b;
+        blk_ct(zb, mu, ct);
+        for (int a = 0; a < 3; ++a) {
+          const double v = hu[3 * b + a] + gs[3 * b + a] + ct[a];
+          rd[3 * b + a] = v;
+          rdinf = fmax(rdinf, fabs(v));
+        }
+        for (int r = 0; r < 5; ++r) sz += s[r] * zb[r];
+        const double w0 = zb[0] / s[0], w1 = zb[1] / s[1], w2 = zb[2] / s[2], w3 = zb[3] / s[3], w4 = zb[4] / s[4];
+        double* wr = wrow + 9 * b;  // rows 3b..3b+2, 3 entries each
+        wr[0] = w0 + w1; wr[1] = 0.0; wr[2] = mu * (w0 - w1);
+        wr[3] = 0.0; wr[4] = w2 + w3; wr[5] = mu * (w2 - w3);
+        wr[6] = mu * (w0 - w1); wr[7] = mu * (w2 - w3); wr[8] = mu * mu * (w0 + w1 + w2 + w3) + w4;
+      }
+      rdinf = wmax(rdinf);
+      sz = wsum(sz);
+      const double mub = sz / (double)m;
+      if (!(rdinf == rdinf) || !(mub == mub)) { ipm_broken = true; break; }
+      if (rdinf <= rd_tol && mub <= mu_tol) { ipm_converged = true; break; }
+      ++n_ipm;
+      __syncwarp();
+      if (!wfactor<true>(Hg, wrow, n, Lp, lane)) { ipm_broken = true; break; }
+      // predictor
+      double b0 = -(hu[lane] + gs[lane]), b1 = -(hu[lane + 32] + gs[lane + 32]);
+      wsolve(Lp, t8, lane, b0, b1);
+      dua[lane] = b0; dua[lane + 32] = b1;
+      __syncwarp();
+      double amax = 1.0;
+      if (lane < nb) {
+        const int b = lane;
+        double s[5], ds[5];
+        blk_slack(u + 3 * b, mu, fzm, s);
+        blk_dslack(dua + 3 * b, mu, ds);
+        const double* zb = z + 5 * b;
+        for (int r = 0; r < 5; ++r) {
+          const double dz = -zb[r] - (zb[r] / s[r]) * ds[r];
+          if (ds[r] < 0) amax = fmin(amax, -s[r] / ds[r]);
+          if (dz < 0) amax = fmin(amax, -zb[r] / dz);
+        }
+      }
+      amax = wmin(amax);
+      double szaff = 0;
+      if (lane < nb) {
+        const int b = lane;
+        double s[5], ds[5];
+        blk_slack(u + 3 * b, mu, fzm, s);
+        blk_dslack(dua + 3 * b, mu, ds);
+        const double* zb = z + 5 * b;
+        for (int r = 0; r < 5; ++r) {
+          const double dz = -zb[r] - (zb[r] / s[r]) * ds[r];
+          szaff += (s[r] + amax * ds[r]) * (zb[r] + amax * dz);
+        }
+      }
+      szaff = wsum(szaff);
+      const double rat = (szaff / (double)m) / mub;
+      const double sigma = rat * rat * rat;
+      du[lane] = 0.0; du[lane + 32] = 0.0;
+      __syncwarp();
+      if (lane < nb) {
+        const int b = lane;
+        double s[5], ds[5], w[5], ct[3];
+        blk_slack(u + 3 * b, mu, fzm, s);
+        blk_dslack(dua + 3 * b, mu, ds);
+        const double* zb = z + 5 * b;
+        for (int r = 0; r < 5; ++r) {
+          const double dz = -zb[r] - (zb[r] / s[r]) * ds[r];
+          w[r] = (-s[r] * zb[r] + sigma * mub - ds[r] * dz) / s[r];
+        }
+        blk_ct(w, mu, ct);
+        for (int a = 0; a < 3; ++a) du[3 * b + a] = -rd[3 * b + a] - ct[a];
+      }
+      __syncwarp();
+      b0 = du[lane]; b1 = du[lane + 32];
+      wsolve(Lp, t8, lane, b0, b1);
+      __syncwarp();
+      du[lane] = b0; du[lane + 32] = b1;
+      __syncwarp();
+      double a2 = 1e300;
+      double znew[5];
+      if (lane < nb) {
+        const int b = lane;
+        double s[5], dsa[5], ds[5];
+        blk_slack(u + 3 * b, mu, fzm, s);
+        blk_dslack(dua + 3 * b, mu, dsa);
+        blk_dslack(du + 3 * b, mu, ds);
+        const double* zb = z + 5 * b;
+        for (int r = 0; r < 5; ++r) {
+          const double wr = zb[r] / s[r];
+          const double dza = -zb[r] - wr * dsa[r];
+          const double rc = -s[r] * zb[r] + sigma * mub - dsa[r] * dza;
+          const double dz = rc / s[r] - wr * ds[r];
+          if (ds[r] < 0) a2 = fmin(a2, -s[r] / ds[r]);
+          if (dz < 0) a2 = fmin(a2, -zb[r] / dz);
+          znew[r] = dz;
+        }
+      }
+      a2 = wmin(a2);
+      const double alpha = fmin(1.0, 0.995 * a2);
+      if (lane < nb)
+        for (int r = 0; r < 5; ++r) z[5 * lane + r] += alpha * znew[r];
+      u[lane] += alpha * du[lane];
+      u[lane + 32] += alpha * du[lane + 32];
+      __syncwarp();
+    }
+    if (ipm_broken) { status = 3; break; }
+    if (stage == 2) {
+      status = ipm_converged ? 1 : 2;
+      solved = ipm_converged;
+      break;
+    }
+
+    // ---------------- stage 4b: exact active-set polish on the identified pyramid faces
+    {
+      double smax = 0, zmax = 0;
+      double s[5];
+      if (lane < nb) {
+        blk_slack(u + 3 * lane, mu, fzm, s);
+        for (int r = 0; r < 5; ++r) { smax = fmax(smax, s[r]); zmax = fmax(zmax, z[5 * lane + r]); }
+      }
+      smax = wmax(smax);
+      zmax = wmax(zmax);
+      const double bal = smax / (zmax > 1e-300 ? zmax : 1e-300);
+      if (lane < nb) {
+        bool act[5];
+        for (int r = 0; r < 5; ++r) act[r] = s[r] < z[5 * lane + r] * bal;
+        face[4 * lane + 0] = act[0] ? -1 : (act[1] ? 1 : 0);
+        face[4 * lane + 1] = act[2] ? -1 : (act[3] ? 1 : 0);
+        face[4 * lane + 2] = act[4] ? 1 : 0;
+        face[4 * lane + 3] = ((act[0] && act[1]) || (act[2] && act[3])) ? 1 : 0;
+      }
+      __syncwarp();
+    }
+    bool polished = false;
+    for (int round = 0; round < 6; ++round) {
+      ++n_polish;
+      // p (pinned particular solution) in rd ; hu = Hs p
+      rd[lane] = 0.0; rd[lane + 32] = 0.0;
+      __syncwarp();
+      if (lane < nb) {
+        const int b = lane;
+        const int sx = face[4 * b], sy = face[4 * b + 1], top = face[4 * b + 2], apex = face[4 * b + 3];
+        const double pz = (top && !apex) ? fzm : 0.0;
+        rd[3 * b] = sx * mu * pz; rd[3 * b + 1] = sy * mu * pz; rd[3 * b + 2] = pz;
+      }
+      __syncwarp();
+      {
+        double y0, y1;
+        wsymv(Hg, rd, lane, y0, y1);
+        hu[lane] = y0; hu[lane + 32] = y1;
+      }
+      // Mt = T' Hs T with pinned rows/cols replaced by identity, written into the panel storage
+      {
+        const int npairs = (nb * (nb + 1)) >> 1;
+        for (int pr = lane; pr < npairs; pr += 32) {
+          int b1, b2;
+          pair_from_index(pr, b1, b2);
+          double X[9];
+#pragma unroll
+          for (int a1 = 0; a1 < 3; ++a1)
+#pragma unroll
+            for (int a2 = 0; a2 < 3; ++a2) X[a1 + 3 * a2] = __ldcg(Hg + (3 * b2 + a2) * WN + 3 * b1 + a1);
+          const double s1x = mu * face[4 * b1], s1y = mu * face[4 * b1 + 1];
+          const double s2x = mu * face[4 * b2], s2y = mu * face[4 * b2 + 1];
+#pragma unroll
+          for (int a2 = 0; a2 < 3; ++a2) X[2 + 3 * a2] += s1x * X[0 + 3 * a2] + s1y * X[1 + 3 * a2];
+#pragma unroll
+          for (int a1 = 0; a1 < 3; ++a1) X[a1 + 6] += s2x * X[a1] + s2y * X[a1 + 3];
+          const int ap1 = face[4 * b1 + 3], ap2 = face[4 * b2 + 3];
+          const bool pin1[3] = {ap1 || face[4 * b1] != 0, ap1 || face[4 * b1 + 1] != 0, ap1 || face[4 * b1 + 2] != 0};
+          const bool pin2[3] = {ap2 || face[4 * b2] != 0, ap2 || face[4 * b2 + 1] != 0, ap2 || face[4 * b2 + 2] != 0};
+#pragma unroll
+          for (int a1 = 0; a1 < 3; ++a1)
+#pragma unroll
+            for (int a2 = 0; a2 < 3; ++a2) {
+              const int r = 3 * b1 + a1, c = 3 * b2 + a2;
+              if (c <= r) {
+                double v = X[a1 + 3 * a2];
+                if (pin1[a1] || pin2[a2]) v = (r == c) ? 1.0 : 0.0;
+                Lp[wp_addr(r, c)] = v;
+              }
+            }
+        }
+        // identity padding rows n..63
+        for (int r = n; r < WN; ++r)
+          for (int c = lane; c <= r; c += 32) Lp[wp_addr(r, c)] = (r == c) ? 1.0 : 0.0;
+      }
+      __syncwarp();
+      du[lane] = 0.0; du[lane + 32] = 0.0;
+      __syncwarp();
+      if (lane < nb) {
+        const int b = lane;
+        const int sx = face[4 * b], sy = face[4 * b + 1], top = face[4 * b + 2], apex = face[4 * b + 3];
+        const double gx = gs[3 * b] + hu[3 * b], gy = gs[3 * b + 1] + hu[3 * b + 1], gz = gs[3 * b + 2] + hu[3 * b + 2];
+        const double gzt = gz + mu * (sx * gx + sy * gy);
+        du[3 * b] = (apex || sx != 0) ? 0.0 : -gx;
+        du[3 * b + 1] = (apex || sy != 0) ? 0.0 : -gy;
+        du[3 * b + 2] = (apex || top) ? 0.0 : -gzt;
+      }
+      __syncwarp();
+      if (!wfactor<false>(Hg, wrow, n, Lp, lane)) break;
+      double b0 = du[lane], b1 = du[lane + 32];
+      wsolve(Lp, t8, lane, b0, b1);
+      __syncwarp();
+      du[lane] = b0; du[lane + 32] = b1;
+      dua[lane] = 0.0; dua[lane + 32] = 0.0;
+      __syncwarp();
+      if (lane < nb) {
+        const int b = lane;
+        const int sx = face[4 * b], sy = face[4 * b + 1];
+        const double vx = du[3 * b], vy = du[3 * b + 1], vz = du[3 * b + 2];
+        dua[3 * b] = vx + mu * sx * vz + rd[3 * b];
+        dua[3 * b + 1] = vy + mu * sy * vz + rd[3 * b + 1];
+        dua[3 * b + 2] = vz + rd[3 * b + 2];
+      }
+      __syncwarp();
+      {
+        double y0, y1;
+        wsymv(Hg, dua, lane, y0, y1);
+        hu[lane] = y0; hu[lane + 32] = y1;
+      }
+      __syncwarp();
+      int changed = 0;
+      if (lane < nb) {
+        const int b = lane;
+        int sx = face[4 * b], sy = face[4 * b + 1], top = face[4 * b + 2], apex = face[4 * b + 3];
+        const double gx = hu[3 * b] + gs[3 * b], gy = hu[3 * b + 1] + gs[3 * b + 1], gz = hu[3 * b + 2] + gs[3 * b + 2];
+        const double fx = dua[3 * b], fy = dua[3 * b + 1], fz = dua[3 * b + 2];
+        if (apex) {
+          if (gz < mu * (fabs(gx) + fabs(gy)) - dual_tol) {
+            apex = 0; top = 0;
+            sx = gx > 0 ? -1 : (gx < 0 ? 1 : 0);
+            sy = gy > 0 ? -1 : (gy < 0 ? 1 : 0);
+            changed = 1;
+          }
+        } else {
+          const double gvz = gz + mu * (sx * gx + sy * gy);
+          const bool dropx = sx != 0 && ((sx == -1 ? gx : -gx) < -dual_tol);
+          const bool dropy = sy != 0 && ((sy == -1 ? gy : -gy) < -dual_tol);
+          const bool dropt = top && (-gvz < -dual_tol);
+          int nsx = dropx ? 0 : sx, nsy = dropy ? 0 : sy, ntop = dropt ? 0 : top, napex = 0;
+          if (fz > fzm + feas_tol) ntop = 1;
+          if (fz < -feas_tol) napex = 1;
+          else {
+            if (sx == 0) { if (-fx - mu * fz > feas_tol) nsx = -1; else if (fx - mu * fz > feas_tol) nsx = 1; }
+            if (sy == 0) { if (-fy - mu * fz > feas_tol) nsy = -1; else if (fy - mu * fz > feas_tol) nsy = 1; }
+          }
+          if (nsx != sx || nsy != sy || ntop != top || napex != apex) changed = 1;
+          sx = nsx; sy = nsy; top = ntop; apex = napex;
+        }
+        face[4 * b] = (signed char)sx; face[4 * b + 1] = (signed char)sy; face[4 * b + 2] = (signed char)top; face[4 * b + 3] = (signed char)apex;
+      }
+      const bool any_changed = __any_sync(0xffffffffu, changed);
+      __syncwarp();
+      if (!any_changed) { polished = true; break; }
+    }
+    if (polished) {
+      u[lane] = dua[lane]; u[lane + 32] = dua[lane + 32];
+      __syncwarp();
+      status = 0;
+      solved = true;
+    }
+  }
+  if (status < 0) status = 2;
+
+  // ---------------- stage 5: outputs
+  const bool ok = status < 2;
+  {
+    double* Uout = Bt.U ? Bt.U + (size_t)(12 * H) * p64 : nullptr;
+    if (Uout) {
+      for (int i = lane; i < 12 * H; i += 32) {
+        const int b = bmap[i / 3];
+        Uout[i] = (b >= 0 && ok) ? u[3 * b + i % 3] : 0.0;
+      }
+    }
+    if (lane < 12) {
+      const int b = bmap[lane / 3];  // step 0, leg lane/3
+      Bt.grf[12 * p64 + lane] = (b >= 0 && ok) ? u[3 * b + lane % 3] : 0.0;
+    }
+    if (Bt.active) {
+      unsigned int* aw = reinterpret_cast<unsigned int*>(wrow);  // scratch (W <= 24 words)
+      __syncwarp();
+      for (int w = lane; w < W; w += 32) aw[w] = 0u;
+      __syncwarp();
+      for (int idx = lane; idx < 4 * H; idx += 32) {
+        const int k = idx >> 2, l = idx & 3;
+        double f0 = 0, f1 = 0, f2 = 0, ub = 0;
+        const int b = bmap[idx];
+        if (b >= 0) {
+          ub = fzm;
+          if (ok) { f0 = u[3 * b]; f1 = u[3 * b + 1]; f2 = u[3 * b + 2]; }
+        }
+        const double res[6] = {f0 + mu * f2, -(f0 - mu * f2), f1 + mu * f2, -(f1 - mu * f2), f2, ub - f2};
+        const int bits[6] = {16 * k + 4 * l + 0, 16 * k + 4 * l + 1, 16 * k + 4 * l + 2, 16 * k + 4 * l + 3,
+                             16 * H + 4 * k + l, 20 * H + 4 * k + l};
+        for (int t = 0; t < 6; ++t)
+          if (fabs(res[t]) <= P.act_tol) atomicOr(&aw[bits[t] >> 5], 1u << (bits[t] & 31));
+      }
+      __syncwarp();
+      for (int w = lane; w < W; w += 32) Bt.active[(size_t)W * p64 + w] = aw[w];
+    }
+    if (lane == 0) {
+      const int nf = n_ipm + n_polish;
+      if (Bt.status) Bt.status[p64] = status;
+      if (Bt.iters) Bt.iters[p64] = (nf & 0xffff) | (n_polish << 16);
+    }
+    const int nf = n_ipm + n_polish;
+    ws.problems++; ws.sum_n += n; ws.sum_fact += nf; ws.sum_polish += n_polish;
+    if (status >= 2) ws.not_ok++;
+    if (status == 1) ws.ipm_only++;
+    const double dn = (double)n;
+    ws.flops += (double)nf * (dn * dn * dn / 3.0) + (double)n_ipm * (4.0 * dn * dn + 2.0 * dn * dn) +
+                (double)n_polish * (2.0 * dn * dn + 4.0 * dn * dn);
+  }
+  __syncwarp();
+}
+
+}  // namespace lmpc
