@@ -52,7 +52,7 @@ __global__ void classify_kernel(const uint8_t* __restrict__ contact, int H, int 
 // Persistent one-warp-per-QP solve (class A).  One warp per CTA: no block barrier exists in this
 // kernel.  Problems are handed out by an atomic counter; the scaled Hessian of the problem in
 // flight lives in this CTA's 32 KB slot of the L2-resident workspace `gws`.
-__global__ void __launch_bounds__(32) solve_warp_kernel(const __grid_constant__ KParams P,
+__global__ void __launch_bounds__(32, 9) solve_warp_kernel(const __grid_constant__ KParams P,
                                                         const __grid_constant__ KBatch Bt,
                                                         KStats* stats, double* gws,
                                                         const int* __restrict__ count,

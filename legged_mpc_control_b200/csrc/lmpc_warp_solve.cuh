@@ -1,12 +1,46 @@
 // lmpc_warp_solve.cuh — one-warp-per-QP driver (n <= 64): same algorithm and formulas as
 // solve_one() in lmpc_solver.cuh (SRBD build -> discretise -> structured condense -> Mehrotra
-// interior point -> exact active-set polish), re-mapped onto a single warp with the dense
-// kernels of lmpc_warp.cuh.  Reference citations as in lmpc_solver.cuh.
+// interior point -> exact active-set polish), re-mapped onto a single warp with the FP64
+// tensor-core dense kernels of lmpc_wmma.cuh.  Reference citations as in lmpc_solver.cuh.
 #pragma once
 #include "lmpc_solver.cuh"
-#include "lmpc_warp.cuh"
+#include "lmpc_wmma.cuh"
 
 namespace lmpc {
+
+// shared-memory plan of one warp (offsets in doubles, then bytes).  The setup scratch (SRBD
+// build, free response, gradient pieces) is dead before the factor is first written and aliases it.
+struct WarpPlan {
+  int oLS, oU, oGS, oZ, oPRM, oHU, oRD, oDUA, oDU, oWROW;  // doubles
+  int oBW, oCOS, oSIN, oCS, oSS, oE, oAJ, oBJ;             // setup, inside LS
+  int n_doubles;
+  int oBLK, oFACE, oBMAP, total_bytes;
+};
+__host__ __device__ inline WarpPlan make_warp_plan(int H) {
+  WarpPlan p;
+  int s = 0;
+  p.oLS = 0;
+  p.oBW = s; s += 36;
+  p.oCOS = s; s += H; p.oSIN = s; s += H; p.oCS = s; s += H; p.oSS = s; s += H;
+  p.oE = s; s += 12 * H; p.oAJ = s; s += 3 * H; p.oBJ = s; s += 3 * H;
+  int o = s > WLS ? s : WLS;
+  p.oU = o; o += WN;
+  p.oGS = o; o += WN;
+  p.oHU = o; o += WN;
+  p.oRD = o; o += WN;
+  p.oDUA = o; o += WN;
+  p.oDU = o; o += WN;
+  p.oWROW = o; o += 3 * WN;
+  p.oZ = o; o += 112;
+  p.oPRM = o; o += 32;
+  p.n_doubles = o;
+  int b = o * 8;
+  p.oBLK = b; b += 2 * 24;
+  p.oFACE = b; b += 4 * 24;
+  p.oBMAP = b; b += 2 * 4 * H;
+  p.total_bytes = (b + 15) & ~15;
+  return p;
+}
 
 struct WarpStats {
   unsigned long long problems = 0, sum_n = 0, sum_fact = 0, sum_polish = 0, not_ok = 0, ipm_only = 0;
@@ -71,12 +105,11 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
   const int lane = threadIdx.x & 31;
   const int H = P.H;
   double* sd = reinterpret_cast<double*>(smem);
-  double* Lp = sd + pl.oLP;
+  double* Ls = sd + pl.oLS;
   double* u = sd + pl.oU;
   double* gs = sd + pl.oGS;
   double* z = sd + pl.oZ;
   double* prm = sd + pl.oPRM;
-  double* t8 = sd + pl.oT8;
   double* hu = sd + pl.oHU;
   double* rd = sd + pl.oRD;
   double* dua = sd + pl.oDUA;
@@ -238,8 +271,8 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
     // identity padding for rows/cols >= n
     for (int idx = lane; idx < WN * (WN - n); idx += 32) {
       const int c = n + idx / WN, r = idx % WN;
-      __stcg(Hg + c * WN + r, (r == c) ? 1.0 : 0.0);
-      __stcg(Hg + r * WN + c, (r == c) ? 1.0 : 0.0);
+      __stcg(Hg + hfull_off(r, c), (r == c) ? 1.0 : 0.0);
+      __stcg(Hg + hfull_off(c, r), (r == c) ? 1.0 : 0.0);
     }
     const int npairs = (nb * (nb + 1)) >> 1;
     for (int pr = lane; pr < npairs; pr += 32) {
@@ -254,8 +287,8 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
         for (int a2 = 0; a2 < 3; ++a2) {
           const int r = 3 * b1 + a1, c = 3 * b2 + a2;
           const double v = sc * o[a1 + 3 * a2];
-          __stcg(Hg + c * WN + r, v);
-          __stcg(Hg + r * WN + c, v);  // (diagonal blocks are symmetric, so the double write agrees)
+          __stcg(Hg + hfull_off(r, c), v);
+          __stcg(Hg + hfull_off(c, r), v);  // (diagonal blocks are symmetric, so the double write agrees)
         }
     }
     if (lane < nb) {
@@ -283,9 +316,9 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
   for (int i = lane; i < 3 * WN; i += 32) wrow[i] = 0.0;
   __syncwarp();
   {
-    double y0, y1;
-    wsymv(Hg, u, lane, y0, y1);
-    double ginf = wmax(fmax(fabs(y0 + gs[lane]), fabs(y1 + gs[lane + 32])));
+    wm_symv(Hg, u, hu);
+    __syncwarp();
+    double ginf = wmax(fmax(fabs(hu[lane] + gs[lane]), fabs(hu[lane + 32] + gs[lane + 32])));
     double ssum = 0;
     double s[5];
     if (lane < nb) {
@@ -306,9 +339,7 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
     const double mu_tol = stage == 0 ? 1e-7 : (stage == 1 ? 1e-10 : 1e-13);
     bool ipm_converged = false, ipm_broken = false;
     while (n_ipm < max_iter) {
-      double h0, h1;
-      wsymv(Hg, u, lane, h0, h1);
-      hu[lane] = h0; hu[lane + 32] = h1;
+      wm_symv(Hg, u, hu);
       rd[lane] = 0.0; rd[lane + 32] = 0.0;
       __syncwarp();
       double rdinf = 0, sz = 0;
@@ -337,11 +368,11 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
       if (rdinf <= rd_tol && mub <= mu_tol) { ipm_converged = true; break; }
       ++n_ipm;
       __syncwarp();
-      if (!wfactor<true>(Hg, wrow, n, Lp, lane)) { ipm_broken = true; break; }
+      if (!wm_factor<true>(Hg, wrow, n, Ls)) { ipm_broken = true; break; }
       // predictor
-      double b0 = -(hu[lane] + gs[lane]), b1 = -(hu[lane + 32] + gs[lane + 32]);
-      wsolve(Lp, t8, lane, b0, b1);
-      dua[lane] = b0; dua[lane + 32] = b1;
+      dua[lane] = -(hu[lane] + gs[lane]); dua[lane + 32] = -(hu[lane + 32] + gs[lane + 32]);
+      __syncwarp();
+      wm_solve(Ls, dua);
       __syncwarp();
       double amax = 1.0;
       if (lane < nb) {
@@ -388,10 +419,7 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
         for (int a = 0; a < 3; ++a) du[3 * b + a] = -rd[3 * b + a] - ct[a];
       }
       __syncwarp();
-      b0 = du[lane]; b1 = du[lane + 32];
-      wsolve(Lp, t8, lane, b0, b1);
-      __syncwarp();
-      du[lane] = b0; du[lane + 32] = b1;
+      wm_solve(Ls, du);
       __syncwarp();
       double a2 = 1e300;
       double znew[5];
@@ -461,11 +489,8 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
         rd[3 * b] = sx * mu * pz; rd[3 * b + 1] = sy * mu * pz; rd[3 * b + 2] = pz;
       }
       __syncwarp();
-      {
-        double y0, y1;
-        wsymv(Hg, rd, lane, y0, y1);
-        hu[lane] = y0; hu[lane + 32] = y1;
-      }
+      wm_symv(Hg, rd, hu);
+      __syncwarp();
       // Mt = T' Hs T with pinned rows/cols replaced by identity, written into the panel storage
       {
         const int npairs = (nb * (nb + 1)) >> 1;
@@ -476,7 +501,7 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
 #pragma unroll
           for (int a1 = 0; a1 < 3; ++a1)
 #pragma unroll
-            for (int a2 = 0; a2 < 3; ++a2) X[a1 + 3 * a2] = __ldcg(Hg + (3 * b2 + a2) * WN + 3 * b1 + a1);
+            for (int a2 = 0; a2 < 3; ++a2) X[a1 + 3 * a2] = __ldcg(Hg + hfull_off(3 * b1 + a1, 3 * b2 + a2));
           const double s1x = mu * face[4 * b1], s1y = mu * face[4 * b1 + 1];
           const double s2x = mu * face[4 * b2], s2y = mu * face[4 * b2 + 1];
 #pragma unroll
@@ -494,13 +519,17 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
               if (c <= r) {
                 double v = X[a1 + 3 * a2];
                 if (pin1[a1] || pin2[a2]) v = (r == c) ? 1.0 : 0.0;
-                Lp[wp_addr(r, c)] = v;
+                Ls[lfac_off(r, c)] = v;
+                if ((r >> 3) == (c >> 3)) Ls[lfac_off(c, r)] = v;  // diagonal tiles are kept full
               }
             }
         }
         // identity padding rows n..63
         for (int r = n; r < WN; ++r)
-          for (int c = lane; c <= r; c += 32) Lp[wp_addr(r, c)] = (r == c) ? 1.0 : 0.0;
+          for (int c = lane; c <= r; c += 32) {
+            Ls[lfac_off(r, c)] = (r == c) ? 1.0 : 0.0;
+            if ((r >> 3) == (c >> 3)) Ls[lfac_off(c, r)] = (r == c) ? 1.0 : 0.0;
+          }
       }
       __syncwarp();
       du[lane] = 0.0; du[lane + 32] = 0.0;
@@ -515,11 +544,8 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
         du[3 * b + 2] = (apex || top) ? 0.0 : -gzt;
       }
       __syncwarp();
-      if (!wfactor<false>(Hg, wrow, n, Lp, lane)) break;
-      double b0 = du[lane], b1 = du[lane + 32];
-      wsolve(Lp, t8, lane, b0, b1);
-      __syncwarp();
-      du[lane] = b0; du[lane + 32] = b1;
+      if (!wm_factor<false>(Hg, wrow, n, Ls)) break;
+      wm_solve(Ls, du);
       dua[lane] = 0.0; dua[lane + 32] = 0.0;
       __syncwarp();
       if (lane < nb) {
@@ -531,11 +557,7 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
         dua[3 * b + 2] = vz + rd[3 * b + 2];
       }
       __syncwarp();
-      {
-        double y0, y1;
-        wsymv(Hg, dua, lane, y0, y1);
-        hu[lane] = y0; hu[lane + 32] = y1;
-      }
+      wm_symv(Hg, dua, hu);
       __syncwarp();
       int changed = 0;
       if (lane < nb) {

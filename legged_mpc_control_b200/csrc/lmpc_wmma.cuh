@@ -1,0 +1,265 @@
+// lmpc_wmma.cuh — dense FP64 kernels of the one-warp-per-QP path (reduced dimension n <= 64) on
+// the FP64 tensor path (DMMA, mma.sync.aligned.m8n8k4.f64).
+//
+// FRAGMENT LAYOUT.  The padded 64x64 matrices are cut into 8x8 tiles and every tile is kept in the
+// accumulator ("C") layout of the m8n8k4 DMMA:  lane = 4*g + t  (g = lane>>2, t = lane&3) owns
+// the two adjacent elements  tile[g][2t], tile[g][2t+1]  as one double2.  A tile is 32 x 16 B =
+// 512 contiguous bytes ("fragment order"), so a warp moves a tile with ONE conflict-free 128-bit
+// load or store per lane, and a lane only ever re-reads the 16 bytes it wrote itself: the shared
+// memory that holds the Cholesky factor is a private extension of the register file and the
+// factorization needs no warp barrier at all.
+//
+// K-PERMUTATION.  A DMMA sums over 4 k-slots and slot t of operand A meets slot t of operand B.
+// With the slot->k map  k = 2t (first DMMA) and k = 2t+1 (second DMMA), a C-layout register pair
+// of tile X is DIRECTLY the A operand X[g][k] (.x then .y) and DIRECTLY the B operand
+// B[k][n=g] = Y[g][k] of the product X * Y^T.  Every product the Cholesky needs has that shape
+// (L_IK * L_JK^T, A_IJ * inv(L_JJ)^T), so tiles flow accumulator -> operand with no shuffle.
+//
+// Factorization (left-looking by tile columns): per tile column J the 8-J accumulator tiles are
+// initialised with -(H + W), updated with 2 DMMAs per earlier tile column, the diagonal tile is
+// factored and inverted by row elimination with quad/oct shuffles (wm_diag8), and the panel is
+// L_IJ = A_IJ * inv(L_JJ)^T, two more DMMAs per tile.  Diagonal slots store inv(L_JJ)^T, which
+// makes both triangular solves 8x8 block mat-vecs with no layout conversion:
+//   "t-layout": lane holds v[8K+2t], v[8K+2t+1];  "g-layout": lane holds v[8K+g].
+//   tile * t-layout vector -> (sum over t: 2 shuffle stages) -> g-layout
+//   tile^T * g-layout vector -> (sum over g: 3 shuffle stages) -> t-layout
+#pragma once
+#include <cuda_runtime.h>
+#include <math.h>
+#include "lmpc_types.cuh"
+
+namespace lmpc {
+
+constexpr int WN = 64;            // padded dimension of the warp path
+constexpr int WNT = 8;            // tiles per dimension
+constexpr int WNBMAX = 21;        // max stance blocks (3*21 = 63 <= 64)
+constexpr int WLTILES = 36;       // lower-triangular tiles of the factor
+constexpr int WLS = WLTILES * 64; // doubles of factor storage (18 KB)
+constexpr int WHS = 64 * 64;      // doubles of the full-symmetric Hessian workspace (all 64 tiles)
+
+__host__ __device__ constexpr int tri(int r, int c) { return (r * (r + 1)) / 2 + c; }
+
+// offset (in doubles) of element (r, c) inside a fragment-ordered tile array with `tile` index
+__device__ __forceinline__ int frag_off(int tile, int r, int c) {
+  return tile * 64 + (((r & 7) << 2) + ((c & 7) >> 1)) * 2 + (c & 1);
+}
+// full-symmetric Hessian workspace: tile (I, J) at index 8I + J
+__device__ __forceinline__ int hfull_off(int r, int c) { return frag_off(((r >> 3) << 3) + (c >> 3), r, c); }
+// factor storage: lower tiles only, tile (I, J), I >= J at index tri(I, J)
+__device__ __forceinline__ int lfac_off(int r, int c) { return frag_off(tri(r >> 3, c >> 3), r, c); }
+
+__device__ __forceinline__ double wsum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ double wmin(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmin(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ double wmax(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+// sum over the 4 lanes of a quad (over t)
+__device__ __forceinline__ double qsum(double v) {
+  v += __shfl_xor_sync(0xffffffffu, v, 1);
+  v += __shfl_xor_sync(0xffffffffu, v, 2);
+  return v;
+}
+// sum over the 8 quads (over g)
+__device__ __forceinline__ double gsum(double v) {
+  v += __shfl_xor_sync(0xffffffffu, v, 4);
+  v += __shfl_xor_sync(0xffffffffu, v, 8);
+  v += __shfl_xor_sync(0xffffffffu, v, 16);
+  return v;
+}
+
+// 1/a and 1/sqrt(a) from the 20-bit hardware seed + two Newton steps (full double accuracy up to
+// the last ulp; no slow-path branch, a must be a positive normal number).
+__device__ __forceinline__ double frcp(double a) {
+  double x;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(x) : "d"(a));
+  double e = fma(-a, x, 1.0);
+  x = fma(x, e, x);
+  e = fma(-a, x, 1.0);
+  return fma(x, e, x);
+}
+__device__ __forceinline__ double frsqrt(double a) {
+  double x;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(x) : "d"(a));
+  double e = fma(-a * x, x, 1.0);
+  x = fma(0.5 * x, e, x);
+  e = fma(-a * x, x, 1.0);
+  return fma(0.5 * x, e, x);
+}
+
+// c += A-slot a x B-slot b  (one k-chunk of an 8x8x4 FP64 tensor-core product)
+__device__ __forceinline__ void dmma(double2& c, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+               : "+d"(c.x), "+d"(c.y)
+               : "d"(a), "d"(b));
+}
+// c += X * Y^T for two C-layout tiles (both k-chunks)
+__device__ __forceinline__ void dmma_xyt(double2& c, const double2& x, const double2& y) {
+  dmma(c, x.x, y.x);
+  dmma(c, x.y, y.y);
+}
+
+// Factor the SPD 8x8 tile A (C-layout, full symmetric) and return inv(L) (lower triangular,
+// C-layout).  Row elimination: row g -= (A[g][c]/d_c) * row c, applied to A and to E = I, gives
+// E = inv(L_unit); inv(L) = diag(1/sqrt(d)) E.  A non-positive pivot poisons the result with NaN.
+__device__ __noinline__ double2 wm_diag8(double ax, double ay) {
+  const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  double ex = (g == 2 * t) ? 1.0 : 0.0, ey = (g == 2 * t + 1) ? 1.0 : 0.0;
+  double dg = 1.0;
+#pragma unroll
+  for (int c = 0; c < 8; ++c) {
+    const double sel = (c & 1) ? ay : ax;
+    const double d = __shfl_sync(0xffffffffu, sel, 4 * c + (c >> 1));
+    const double ac = __shfl_sync(0xffffffffu, sel, (lane & 28) | (c >> 1));
+    const double rx = __shfl_sync(0xffffffffu, ax, 4 * c + t), ry = __shfl_sync(0xffffffffu, ay, 4 * c + t);
+    if (g == c) dg = d;
+    if (c < 7) {
+      const double fx = __shfl_sync(0xffffffffu, ex, 4 * c + t), fy = __shfl_sync(0xffffffffu, ey, 4 * c + t);
+      const double m = (g > c) ? ac * frcp(d) : 0.0;
+      ax = fma(-m, rx, ax); ay = fma(-m, ry, ay);
+      ex = fma(-m, fx, ex); ey = fma(-m, fy, ey);
+    }
+  }
+  const double rs = (dg > 0.0) ? frsqrt(dg) : __longlong_as_double(0x7ff8000000000000ll);
+  return make_double2(rs * ex, rs * ey);
+}
+
+// transpose of an 8x8 tile in C-layout
+__device__ __forceinline__ double2 tile_transpose(const double2& v, int lane) {
+  const int g = lane >> 2, t = lane & 3;
+  const int s0 = 8 * t + (g >> 1), s1 = s0 + 4;  // lanes holding rows 2t and 2t+1, column pair g>>1
+  const double a0 = __shfl_sync(0xffffffffu, v.x, s0), a1 = __shfl_sync(0xffffffffu, v.y, s0);
+  const double b0 = __shfl_sync(0xffffffffu, v.x, s1), b1 = __shfl_sync(0xffffffffu, v.y, s1);
+  return make_double2((g & 1) ? a1 : a0, (g & 1) ? b1 : b0);
+}
+
+// Factor M = L L'.  FROM_H: M = Hg + blockdiag(W): Hg is the full-symmetric fragment-ordered
+// Hessian workspace in global memory (L2), W the 3x3 pyramid blocks given row-wise in
+// wrow[row][3] (rows >= n carry none).  !FROM_H: the lower tiles of M are already in Ls (diagonal
+// tiles full symmetric).  On exit Ls holds L_IJ (I > J) and inv(L_JJ)' in the diagonal slots.
+// Returns false on a non-positive pivot.
+template <bool FROM_H>
+__device__ __noinline__ bool wm_factor(const double* Hg, const double* wrow, int n, double* Ls) {
+  const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  double2* Lf = reinterpret_cast<double2*>(Ls) + lane;
+  const double2* Hf = reinterpret_cast<const double2*>(Hg) + lane;
+  bool bad = false;
+#pragma unroll
+  for (int J = 0; J < WNT; ++J) {
+    double2 acc[WNT];
+#pragma unroll
+    for (int I = J; I < WNT; ++I) {
+      double2 v;
+      if (FROM_H) {
+        v = __ldcg(Hf + 32 * (8 * I + J));
+        if (I - J <= 1) {  // only these tiles can contain entries of a 3x3 pyramid block
+          const int r = 8 * I + g, c = 8 * J + 2 * t;
+          const int d0 = c - (r / 3) * 3;
+          if (r < n) {
+            if (d0 >= 0 && d0 < 3) v.x += wrow[3 * r + d0];
+            if (d0 >= -1 && d0 < 2) v.y += wrow[3 * r + d0 + 1];
+          }
+        }
+      } else {
+        v = Lf[32 * tri(I, J)];
+      }
+      acc[I] = make_double2(-v.x, -v.y);
+    }
+#pragma unroll
+    for (int K = 0; K < J; ++K) {
+      const double2 bj = Lf[32 * tri(J, K)];
+      dmma_xyt(acc[J], bj, bj);
+#pragma unroll
+      for (int I = J + 1; I < WNT; ++I) {
+        const double2 a = Lf[32 * tri(I, K)];
+        dmma_xyt(acc[I], a, bj);
+      }
+    }
+    const double2 li = wm_diag8(-acc[J].x, -acc[J].y);
+    bad = bad || !(li.x == li.x) || !(li.y == li.y);
+    Lf[32 * tri(J, J)] = tile_transpose(li, lane);
+    const double2 nli = make_double2(-li.x, -li.y);
+#pragma unroll
+    for (int I = J + 1; I < WNT; ++I) {
+      double2 x = make_double2(0.0, 0.0);
+      dmma_xyt(x, acc[I], nli);
+      Lf[32 * tri(I, J)] = x;
+    }
+  }
+  return !__any_sync(0xffffffffu, bad);
+}
+
+// Solve L L' x = b in place on the 64-vector `x` in shared memory.  The caller must __syncwarp()
+// between writing b and this call, and again before reading x.
+__device__ __noinline__ void wm_solve(const double* Ls, double* x) {
+  const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const double2* Lf = reinterpret_cast<const double2*>(Ls) + lane;
+  double yx[WNT], yy[WNT];
+  // forward: L y = b
+#pragma unroll
+  for (int J = 0; J < WNT; ++J) {
+    const double bg = x[8 * J + g];
+    double p0 = 0.0, p1 = 0.0;
+#pragma unroll
+    for (int K = 0; K < J; ++K) {
+      const double2 l = Lf[32 * tri(J, K)];
+      p0 = fma(l.x, yx[K], p0);
+      p1 = fma(l.y, yy[K], p1);
+    }
+    const double r = bg - qsum(p0 + p1);            // g-layout
+    const double2 tt = Lf[32 * tri(J, J)];          // tt[g][j] = inv(L)[j][g]
+    yx[J] = gsum(tt.x * r);                         // y[2t]   = sum_g inv(L)[2t][g] r[g]
+    yy[J] = gsum(tt.y * r);
+  }
+  // backward: L' x = y
+  double xg[WNT];
+#pragma unroll
+  for (int J = WNT - 1; J >= 0; --J) {
+    double p0 = 0.0, p1 = 0.0;
+#pragma unroll
+    for (int I = J + 1; I < WNT; ++I) {
+      const double2 l = Lf[32 * tri(I, J)];
+      p0 = fma(l.x, xg[I], p0);
+      p1 = fma(l.y, xg[I], p1);
+    }
+    double r0 = yx[J], r1 = yy[J];
+    if (J < WNT - 1) { r0 -= gsum(p0); r1 -= gsum(p1); }  // t-layout
+    const double2 tt = Lf[32 * tri(J, J)];                // x[g] = sum_j inv(L)'[g][j] r[j]
+    xg[J] = qsum(fma(tt.x, r0, tt.y * r1));
+    if (t == 0) x[8 * J + g] = xg[J];
+  }
+}
+
+// y = H x for the full-symmetric fragment-ordered Hessian workspace (global, L2 resident);
+// x and y are 64-vectors in shared memory (x != y).  Caller syncs as for wm_solve.
+// Hg is written earlier in the same kernel: loads go through L2 (__ldcg).
+__device__ __noinline__ void wm_symv(const double* Hg, const double* x, double* y) {
+  const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const double2* Hf = reinterpret_cast<const double2*>(Hg) + lane;
+  double2 xt[WNT];
+#pragma unroll
+  for (int J = 0; J < WNT; ++J) xt[J] = *reinterpret_cast<const double2*>(x + 8 * J + 2 * t);
+#pragma unroll
+  for (int I = 0; I < WNT; ++I) {
+    double p0 = 0.0, p1 = 0.0;
+#pragma unroll
+    for (int J = 0; J < WNT; ++J) {
+      const double2 h = __ldcg(Hf + 32 * (8 * I + J));
+      p0 = fma(h.x, xt[J].x, p0);
+      p1 = fma(h.y, xt[J].y, p1);
+    }
+    const double s = qsum(p0 + p1);
+    if (t == 0) y[8 * I + g] = s;
+  }
+}
+
+}  // namespace lmpc
