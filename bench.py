@@ -249,7 +249,7 @@ def run_b200(args):
             "gpu_launches": int(launches),
             "roofline": {
                 "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-                "traffic": None, "kernel": "lmpc::solve_kernel<64>", "kernel_ms": kms,
+                "traffic": None, "kernel": "lmpc::solve_warp_kernel", "kernel_ms": kms,
                 "precision": "fp64", "peak_source": "measured on this GPU by lmpc_microbench_fp64 (MEASURED_PEAKS.json has no FP64 entry)",
                 "fp64_peaks_tflops": peaks,
                 "flops_per_launch_executed": stats["flops_executed"], "mean_n_eff": stats["mean_n_eff"],
