@@ -11,7 +11,7 @@ namespace lmpc {
 // shared-memory plan of one warp (offsets in doubles, then bytes).  The setup scratch (SRBD
 // build, free response, gradient pieces) is dead before the factor is first written and aliases it.
 struct WarpPlan {
-  int oLS, oU, oGS, oZ, oPRM, oHU, oRD, oDUA, oDU, oWROW;  // doubles
+  int oLS, oU, oGS, oZ, oPRM, oHU, oRD, oDUA, oDU, oWROW, oXB;  // doubles
   int oBW, oCOS, oSIN, oCS, oSS, oE, oAJ, oBJ;             // setup, inside LS
   int n_doubles;
   int oBLK, oFACE, oBMAP, total_bytes;
@@ -33,6 +33,7 @@ __host__ __device__ inline WarpPlan make_warp_plan(int H) {
   p.oWROW = o; o += 3 * WN;
   p.oZ = o; o += 112;
   p.oPRM = o; o += 32;
+  p.oXB = o; o += 32;
   p.n_doubles = o;
   int b = o * 8;
   p.oBLK = b; b += 2 * 24;
@@ -115,6 +116,7 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
   double* dua = sd + pl.oDUA;
   double* du = sd + pl.oDU;
   double* wrow = sd + pl.oWROW;
+  double* xb = sd + pl.oXB;
   double* Bw = sd + pl.oBW;
   double* cosv = sd + pl.oCOS;
   double* sinv = sd + pl.oSIN;
@@ -190,6 +192,7 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
   }
   __syncwarp();
   const int n = 3 * nb;
+  const int np = WN;  // padded dimension (identity beyond n)
   const double mu = prm[PRM_MU], fzm = prm[PRM_FZ], mass = prm[PRM_MASS];
   const double* qw = prm + PRM_Q;
   const double* rw = prm + PRM_R;
@@ -269,8 +272,8 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
     dmax = wmax(dmax);
     sc = 1.0 / dmax;
     // identity padding for rows/cols >= n
-    for (int idx = lane; idx < WN * (WN - n); idx += 32) {
-      const int c = n + idx / WN, r = idx % WN;
+    for (int idx = lane; idx < np * (np - n); idx += 32) {
+      const int c = n + idx / np, r = idx % np;
       __stcg(Hg + hfull_off(r, c), (r == c) ? 1.0 : 0.0);
       __stcg(Hg + hfull_off(c, r), (r == c) ? 1.0 : 0.0);
     }
@@ -310,142 +313,135 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
   const int m = 5 * nb;
 
   // ---------------- stage 4a: interior point (feasible start)
+  // Lane b < nb owns stance block b: its force u_b, multipliers z_b and slacks stay in registers.
+  // Ratio form of the step rules (q = ds/s):  -ds/s = -q,  -dz_aff/z = 1 + q,  so the predictor
+  // needs no division; reciprocals come from frcp (rcp.approx + 2 Newton steps).
+  const bool act = lane < nb;
+  const double inv_m = 1.0 / (double)m;
+  double uf[3] = {0.0, 0.0, act ? 0.5 * fzm : 0.0};
+  double zr[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
   u[lane] = 0.0; u[lane + 32] = 0.0;
+  hu[lane] = 0.0; hu[lane + 32] = 0.0;
   __syncwarp();
-  if (lane < nb) u[3 * lane + 2] = 0.5 * fzm;
+  if (act) u[3 * lane + 2] = uf[2];
   for (int i = lane; i < 3 * WN; i += 32) wrow[i] = 0.0;
   __syncwarp();
   {
     wm_symv(Hg, u, hu);
     __syncwarp();
-    double ginf = wmax(fmax(fabs(hu[lane] + gs[lane]), fabs(hu[lane + 32] + gs[lane + 32])));
+    const double ginf = wmax(fmax(fabs(hu[lane] + gs[lane]), fabs(hu[lane + 32] + gs[lane + 32])));
     double ssum = 0;
     double s[5];
-    if (lane < nb) {
-      blk_slack(u + 3 * lane, mu, fzm, s);
-      ssum = s[0] + s[1] + s[2] + s[3] + s[4];
-    }
+    blk_slack(uf, mu, fzm, s);
+    if (act) ssum = s[0] + s[1] + s[2] + s[3] + s[4];
     ssum = wsum(ssum);
-    const double zc = (ginf > 1e-6 ? ginf : 1e-6) * (ssum / (double)m);
-    if (lane < nb)
-      for (int r = 0; r < 5; ++r) z[5 * lane + r] = zc / s[r];
+    const double zc = (ginf > 1e-6 ? ginf : 1e-6) * (ssum * inv_m);
+    if (act)
+#pragma unroll
+      for (int r = 0; r < 5; ++r) zr[r] = zc * frcp(s[r]);
   }
-  __syncwarp();
 
   int n_ipm = 0, n_polish = 0, status = -1;
   const int max_iter = P.max_iter;
   bool solved = false;
+#pragma unroll 1
   for (int stage = 0; stage < 3 && !solved; ++stage) {
     const double mu_tol = stage == 0 ? 1e-7 : (stage == 1 ? 1e-10 : 1e-13);
     bool ipm_converged = false, ipm_broken = false;
+#pragma unroll 1
     while (n_ipm < max_iter) {
       wm_symv(Hg, u, hu);
-      rd[lane] = 0.0; rd[lane + 32] = 0.0;
       __syncwarp();
+      double s[5], is[5], w[5], rdv[3] = {0.0, 0.0, 0.0};
       double rdinf = 0, sz = 0;
-      if (lane < nb) {
-        const int b = lane;
-        double s[5], ct[3];
-        blk_slack(u + 3 * b, mu, fzm, s);
-        const double* zb = z + 5 * b;
-        blk_ct(zb, mu, ct);
+      blk_slack(uf, mu, fzm, s);
+      if (act) {
+        double ct[3];
+        blk_ct(zr, mu, ct);
+#pragma unroll
         for (int a = 0; a < 3; ++a) {
-          const double v = hu[3 * b + a] + gs[3 * b + a] + ct[a];
-          rd[3 * b + a] = v;
-          rdinf = fmax(rdinf, fabs(v));
+          rdv[a] = hu[3 * lane + a] + gs[3 * lane + a] + ct[a];
+          rdinf = fmax(rdinf, fabs(rdv[a]));
         }
-        for (int r = 0; r < 5; ++r) sz += s[r] * zb[r];
-        const double w0 = zb[0] / s[0], w1 = zb[1] / s[1], w2 = zb[2] / s[2], w3 = zb[3] / s[3], w4 = zb[4] / s[4];
-        double* wr = wrow + 9 * b;  // rows 3b..3b+2, 3 entries each
-        wr[0] = w0 + w1; wr[1] = 0.0; wr[2] = mu * (w0 - w1);
-        wr[3] = 0.0; wr[4] = w2 + w3; wr[5] = mu * (w2 - w3);
-        wr[6] = mu * (w0 - w1); wr[7] = mu * (w2 - w3); wr[8] = mu * mu * (w0 + w1 + w2 + w3) + w4;
+#pragma unroll
+        for (int r = 0; r < 5; ++r) {
+          is[r] = frcp(s[r]);
+          w[r] = zr[r] * is[r];
+          sz = fma(s[r], zr[r], sz);
+        }
+        double* wr = wrow + 9 * lane;  // rows 3b..3b+2 of C_b' W C_b, 3 entries each
+        wr[0] = w[0] + w[1]; wr[1] = 0.0; wr[2] = mu * (w[0] - w[1]);
+        wr[3] = 0.0; wr[4] = w[2] + w[3]; wr[5] = mu * (w[2] - w[3]);
+        wr[6] = wr[2]; wr[7] = wr[5]; wr[8] = mu * mu * (w[0] + w[1] + w[2] + w[3]) + w[4];
       }
       rdinf = wmax(rdinf);
       sz = wsum(sz);
-      const double mub = sz / (double)m;
+      const double mub = sz * inv_m;
       if (!(rdinf == rdinf) || !(mub == mub)) { ipm_broken = true; break; }
       if (rdinf <= rd_tol && mub <= mu_tol) { ipm_converged = true; break; }
       ++n_ipm;
-      __syncwarp();
-      if (!wm_factor<true>(Hg, wrow, n, Ls)) { ipm_broken = true; break; }
-      // predictor
+      // predictor: (H + C'WC) du_aff = -(H u + g)
       dua[lane] = -(hu[lane] + gs[lane]); dua[lane + 32] = -(hu[lane + 32] + gs[lane + 32]);
-      __syncwarp();
-      wm_solve(Ls, dua);
-      __syncwarp();
-      double amax = 1.0;
-      if (lane < nb) {
-        const int b = lane;
-        double s[5], ds[5];
-        blk_slack(u + 3 * b, mu, fzm, s);
-        blk_dslack(dua + 3 * b, mu, ds);
-        const double* zb = z + 5 * b;
-        for (int r = 0; r < 5; ++r) {
-          const double dz = -zb[r] - (zb[r] / s[r]) * ds[r];
-          if (ds[r] < 0) amax = fmin(amax, -s[r] / ds[r]);
-          if (dz < 0) amax = fmin(amax, -zb[r] / dz);
-        }
-      }
-      amax = wmin(amax);
-      double szaff = 0;
-      if (lane < nb) {
-        const int b = lane;
-        double s[5], ds[5];
-        blk_slack(u + 3 * b, mu, fzm, s);
-        blk_dslack(dua + 3 * b, mu, ds);
-        const double* zb = z + 5 * b;
-        for (int r = 0; r < 5; ++r) {
-          const double dz = -zb[r] - (zb[r] / s[r]) * ds[r];
-          szaff += (s[r] + amax * ds[r]) * (zb[r] + amax * dz);
-        }
-      }
-      szaff = wsum(szaff);
-      const double rat = (szaff / (double)m) / mub;
-      const double sigma = rat * rat * rat;
       du[lane] = 0.0; du[lane + 32] = 0.0;
       __syncwarp();
-      if (lane < nb) {
-        const int b = lane;
-        double s[5], ds[5], w[5], ct[3];
-        blk_slack(u + 3 * b, mu, fzm, s);
-        blk_dslack(dua + 3 * b, mu, ds);
-        const double* zb = z + 5 * b;
+      if (!wm_factor<true>(Hg, wrow, n, Ls, xb)) { ipm_broken = true; break; }
+      wm_solve(Ls, dua);
+      __syncwarp();
+      double q[5], tau = 0.0;
+      if (act) {
+        double dsa[5];
+        blk_dslack(dua + 3 * lane, mu, dsa);
+#pragma unroll
         for (int r = 0; r < 5; ++r) {
-          const double dz = -zb[r] - (zb[r] / s[r]) * ds[r];
-          w[r] = (-s[r] * zb[r] + sigma * mub - ds[r] * dz) / s[r];
+          q[r] = dsa[r] * is[r];
+          tau = fmax(tau, fmax(-q[r], 1.0 + q[r]));
         }
-        blk_ct(w, mu, ct);
-        for (int a = 0; a < 3; ++a) du[3 * b + a] = -rd[3 * b + a] - ct[a];
+      }
+      tau = wmax(tau);
+      const double amax = tau > 1.0 ? frcp(tau) : 1.0;
+      double szaff = 0;
+      if (act)
+#pragma unroll
+        for (int r = 0; r < 5; ++r)
+          szaff = fma(s[r] * zr[r], fma(amax, q[r], 1.0) * (1.0 - amax * (1.0 + q[r])), szaff);
+      szaff = wsum(szaff);
+      const double rat = szaff * frcp(sz);
+      const double smu = rat * rat * rat * mub;  // sigma * mu
+      // corrector: rhs = -rd - C'((sigma mu - ds_aff dz_aff - s z)/s)
+      double w2[5];
+      if (act) {
+        double ct[3];
+#pragma unroll
+        for (int r = 0; r < 5; ++r) w2[r] = fma(zr[r], fma(q[r], 1.0 + q[r], -1.0), smu * is[r]);
+        blk_ct(w2, mu, ct);
+#pragma unroll
+        for (int a = 0; a < 3; ++a) du[3 * lane + a] = -rdv[a] - ct[a];
       }
       __syncwarp();
       wm_solve(Ls, du);
       __syncwarp();
-      double a2 = 1e300;
-      double znew[5];
-      if (lane < nb) {
-        const int b = lane;
-        double s[5], dsa[5], ds[5];
-        blk_slack(u + 3 * b, mu, fzm, s);
-        blk_dslack(dua + 3 * b, mu, dsa);
-        blk_dslack(du + 3 * b, mu, ds);
-        const double* zb = z + 5 * b;
+      double dz[5], duf[3] = {0.0, 0.0, 0.0}, tau2 = 0.0;
+      if (act) {
+        double ds[5];
+#pragma unroll
+        for (int a = 0; a < 3; ++a) duf[a] = du[3 * lane + a];
+        blk_dslack(duf, mu, ds);
+#pragma unroll
         for (int r = 0; r < 5; ++r) {
-          const double wr = zb[r] / s[r];
-          const double dza = -zb[r] - wr * dsa[r];
-          const double rc = -s[r] * zb[r] + sigma * mub - dsa[r] * dza;
-          const double dz = rc / s[r] - wr * ds[r];
-          if (ds[r] < 0) a2 = fmin(a2, -s[r] / ds[r]);
-          if (dz < 0) a2 = fmin(a2, -zb[r] / dz);
-          znew[r] = dz;
+          dz[r] = fma(-w[r], ds[r], w2[r]);
+          tau2 = fmax(tau2, fmax(-ds[r] * is[r], -dz[r] * frcp(zr[r])));
         }
       }
-      a2 = wmin(a2);
-      const double alpha = fmin(1.0, 0.995 * a2);
-      if (lane < nb)
-        for (int r = 0; r < 5; ++r) z[5 * lane + r] += alpha * znew[r];
-      u[lane] += alpha * du[lane];
-      u[lane + 32] += alpha * du[lane + 32];
+      tau2 = wmax(tau2);
+      const double alpha = tau2 > 0.995 ? 0.995 * frcp(tau2) : 1.0;
+      if (act) {
+#pragma unroll
+        for (int r = 0; r < 5; ++r) zr[r] = fma(alpha, dz[r], zr[r]);
+#pragma unroll
+        for (int a = 0; a < 3; ++a) uf[a] = fma(alpha, duf[a], uf[a]);
+      }
+      u[lane] = fma(alpha, du[lane], u[lane]);
+      u[lane + 32] = fma(alpha, du[lane + 32], u[lane + 32]);
       __syncwarp();
     }
     if (ipm_broken) { status = 3; break; }
@@ -459,20 +455,19 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
     {
       double smax = 0, zmax = 0;
       double s[5];
-      if (lane < nb) {
-        blk_slack(u + 3 * lane, mu, fzm, s);
-        for (int r = 0; r < 5; ++r) { smax = fmax(smax, s[r]); zmax = fmax(zmax, z[5 * lane + r]); }
-      }
+      blk_slack(uf, mu, fzm, s);
+      if (act)
+        for (int r = 0; r < 5; ++r) { smax = fmax(smax, s[r]); zmax = fmax(zmax, zr[r]); }
       smax = wmax(smax);
       zmax = wmax(zmax);
       const double bal = smax / (zmax > 1e-300 ? zmax : 1e-300);
       if (lane < nb) {
-        bool act[5];
-        for (int r = 0; r < 5; ++r) act[r] = s[r] < z[5 * lane + r] * bal;
-        face[4 * lane + 0] = act[0] ? -1 : (act[1] ? 1 : 0);
-        face[4 * lane + 1] = act[2] ? -1 : (act[3] ? 1 : 0);
-        face[4 * lane + 2] = act[4] ? 1 : 0;
-        face[4 * lane + 3] = ((act[0] && act[1]) || (act[2] && act[3])) ? 1 : 0;
+        bool actr[5];
+        for (int r = 0; r < 5; ++r) actr[r] = s[r] < zr[r] * bal;
+        face[4 * lane + 0] = actr[0] ? -1 : (actr[1] ? 1 : 0);
+        face[4 * lane + 1] = actr[2] ? -1 : (actr[3] ? 1 : 0);
+        face[4 * lane + 2] = actr[4] ? 1 : 0;
+        face[4 * lane + 3] = ((actr[0] && actr[1]) || (actr[2] && actr[3])) ? 1 : 0;
       }
       __syncwarp();
     }
@@ -525,7 +520,7 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
             }
         }
         // identity padding rows n..63
-        for (int r = n; r < WN; ++r)
+        for (int r = n; r < np; ++r)
           for (int c = lane; c <= r; c += 32) {
             Ls[lfac_off(r, c)] = (r == c) ? 1.0 : 0.0;
             if ((r >> 3) == (c >> 3)) Ls[lfac_off(c, r)] = (r == c) ? 1.0 : 0.0;
@@ -544,7 +539,7 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
         du[3 * b + 2] = (apex || top) ? 0.0 : -gzt;
       }
       __syncwarp();
-      if (!wm_factor<false>(Hg, wrow, n, Ls)) break;
+      if (!wm_factor<false>(Hg, wrow, n, Ls, xb)) break;
       wm_solve(Ls, du);
       dua[lane] = 0.0; dua[lane + 32] = 0.0;
       __syncwarp();

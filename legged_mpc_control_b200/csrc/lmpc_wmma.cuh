@@ -48,17 +48,17 @@ __device__ __forceinline__ int hfull_off(int r, int c) { return frag_off(((r >> 
 // factor storage: lower tiles only, tile (I, J), I >= J at index tri(I, J)
 __device__ __forceinline__ int lfac_off(int r, int c) { return frag_off(tri(r >> 3, c >> 3), r, c); }
 
-__device__ __forceinline__ double wsum(double v) {
+__device__ __noinline__ double wsum(double v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
   return v;
 }
-__device__ __forceinline__ double wmin(double v) {
+__device__ __noinline__ double wmin(double v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v = fmin(v, __shfl_xor_sync(0xffffffffu, v, o));
   return v;
 }
-__device__ __forceinline__ double wmax(double v) {
+__device__ __noinline__ double wmax(double v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
   return v;
@@ -98,7 +98,7 @@ __device__ __forceinline__ double frsqrt(double a) {
 
 // c += A-slot a x B-slot b  (one k-chunk of an 8x8x4 FP64 tensor-core product)
 __device__ __forceinline__ void dmma(double2& c, double a, double b) {
-  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+  asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
                : "+d"(c.x), "+d"(c.y)
                : "d"(a), "d"(b));
 }
@@ -108,47 +108,67 @@ __device__ __forceinline__ void dmma_xyt(double2& c, const double2& x, const dou
   dmma(c, x.y, y.y);
 }
 
+
+// ---- vectors.  A 64-vector block v[8K..8K+7] lives in registers in "t-layout": lane (g, t) holds
+// the pair v[8K+2t], v[8K+2t+1], replicated over g.  That pair is directly the A operand of a
+// DMMA whose rows are all equal to v, so
+//   tile * v   = dmma_xyt(0, v, tile)           (tile read in C-layout, one LDS.128)
+//   tile' * v  = dmma_xyt(0, v, tile^T)         (tile read transposed, two LDS.64)
+// both return their result in t-layout again: triangular solves and H*x run on the tensor pipe
+// with no shuffle and no layout conversion (1/8 of the DMMA's MACs are useful, the FP64 pipe is
+// otherwise idle in those phases).
+
+// transposed read of a fragment-ordered tile: returns {T[2t][g], T[2t+1][g]}
+__device__ __forceinline__ double2 tile_ld_t(const double* tile, int g, int t) {
+  const double* p = tile + 16 * t + g;
+  return make_double2(p[0], p[8]);
+}
+
 // Factor the SPD 8x8 tile A (C-layout, full symmetric) and return inv(L) (lower triangular,
 // C-layout).  Row elimination: row g -= (A[g][c]/d_c) * row c, applied to A and to E = I, gives
-// E = inv(L_unit); inv(L) = diag(1/sqrt(d)) E.  A non-positive pivot poisons the result with NaN.
-__device__ __noinline__ double2 wm_diag8(double ax, double ay) {
+// E = inv(L_unit); inv(L) = diag(1/sqrt(d)) E.  The pivot row travels through a 2 x 16-double
+// shared-memory buffer `xb` (A row | E row, double-buffered by column parity): one predicated
+// 128-bit store pair and four broadcast loads per column instead of twelve 32-bit shuffles.  The
+// trailing matrix stays symmetric, so A[g][c] is read as A[c][g] from the same row.  A
+// non-positive pivot poisons the result with NaN.
+__device__ __noinline__ double2 wm_diag8(double ax, double ay, double* xb) {
   const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   double ex = (g == 2 * t) ? 1.0 : 0.0, ey = (g == 2 * t + 1) ? 1.0 : 0.0;
   double dg = 1.0;
+  double2* xs = reinterpret_cast<double2*>(xb) + t;   // this lane's column pair inside a row
+  const double* xg = xb + g;
 #pragma unroll
-  for (int c = 0; c < 8; ++c) {
-    const double sel = (c & 1) ? ay : ax;
-    const double d = __shfl_sync(0xffffffffu, sel, 4 * c + (c >> 1));
-    const double ac = __shfl_sync(0xffffffffu, sel, (lane & 28) | (c >> 1));
-    const double rx = __shfl_sync(0xffffffffu, ax, 4 * c + t), ry = __shfl_sync(0xffffffffu, ay, 4 * c + t);
-    if (g == c) dg = d;
-    if (c < 7) {
-      const double fx = __shfl_sync(0xffffffffu, ex, 4 * c + t), fy = __shfl_sync(0xffffffffu, ey, 4 * c + t);
-      const double m = (g > c) ? ac * frcp(d) : 0.0;
-      ax = fma(-m, rx, ax); ay = fma(-m, ry, ay);
-      ex = fma(-m, fx, ex); ey = fma(-m, fy, ey);
+  for (int c = 0; c < 7; ++c) {
+    const int o = 16 * (c & 1);
+    if (g == c) {
+      xs[o / 2] = make_double2(ax, ay);
+      xs[o / 2 + 4] = make_double2(ex, ey);
     }
+    __syncwarp();
+    const double d = xb[o + c];
+    const double acg = xg[o];
+    const double2 r = xs[o / 2];
+    const double2 f = xs[o / 2 + 4];
+    if (g == c) dg = d;
+    const double m = (g > c) ? acg * frcp(d) : 0.0;
+    ax = fma(-m, r.x, ax); ay = fma(-m, r.y, ay);
+    ex = fma(-m, f.x, ex); ey = fma(-m, f.y, ey);
   }
+  const double d7 = __shfl_sync(0xffffffffu, ay, 31);  // last pivot A[7][7] lives in lane (7, 3)
+  if (g == 7) dg = d7;
   const double rs = (dg > 0.0) ? frsqrt(dg) : __longlong_as_double(0x7ff8000000000000ll);
   return make_double2(rs * ex, rs * ey);
 }
 
-// transpose of an 8x8 tile in C-layout
-__device__ __forceinline__ double2 tile_transpose(const double2& v, int lane) {
-  const int g = lane >> 2, t = lane & 3;
-  const int s0 = 8 * t + (g >> 1), s1 = s0 + 4;  // lanes holding rows 2t and 2t+1, column pair g>>1
-  const double a0 = __shfl_sync(0xffffffffu, v.x, s0), a1 = __shfl_sync(0xffffffffu, v.y, s0);
-  const double b0 = __shfl_sync(0xffffffffu, v.x, s1), b1 = __shfl_sync(0xffffffffu, v.y, s1);
-  return make_double2((g & 1) ? a1 : a0, (g & 1) ? b1 : b0);
-}
-
-// Factor M = L L'.  FROM_H: M = Hg + blockdiag(W): Hg is the full-symmetric fragment-ordered
-// Hessian workspace in global memory (L2), W the 3x3 pyramid blocks given row-wise in
-// wrow[row][3] (rows >= n carry none).  !FROM_H: the lower tiles of M are already in Ls (diagonal
-// tiles full symmetric).  On exit Ls holds L_IJ (I > J) and inv(L_JJ)' in the diagonal slots.
+// Factor M = L L' (64 x 64, 8 x 8 tiles).  FROM_H: M = Hg + blockdiag(W): Hg is the
+// full-symmetric fragment-ordered Hessian workspace in global memory (L2), W the 3x3 pyramid
+// blocks given row-wise in wrow[row][3] (rows >= n carry none).  !FROM_H: the lower tiles of M
+// are already in Ls (diagonal tiles full symmetric).  On exit Ls holds L_IJ (I > J) and inv(L_JJ)
+// in the diagonal slots.  Left-looking by tile columns: J unrolled (static accumulator indices),
+// the K loop rolled to keep the hot loop inside the instruction cache.
 // Returns false on a non-positive pivot.
 template <bool FROM_H>
-__device__ __noinline__ bool wm_factor(const double* Hg, const double* wrow, int n, double* Ls) {
+__device__ __noinline__ bool wm_factor(const double* Hg, const double* wrow, int n, double* Ls, double* xb) {
   const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   double2* Lf = reinterpret_cast<double2*>(Ls) + lane;
   const double2* Hf = reinterpret_cast<const double2*>(Hg) + lane;
@@ -174,19 +194,19 @@ __device__ __noinline__ bool wm_factor(const double* Hg, const double* wrow, int
       }
       acc[I] = make_double2(-v.x, -v.y);
     }
+    if (J > 0) {
+      const double2* rowJ = Lf + 32 * tri(J, 0);
+#pragma unroll 1
+      for (int K = 0; K < J; ++K) {
+        const double2 bj = rowJ[32 * K];
+        dmma_xyt(acc[J], bj, bj);
 #pragma unroll
-    for (int K = 0; K < J; ++K) {
-      const double2 bj = Lf[32 * tri(J, K)];
-      dmma_xyt(acc[J], bj, bj);
-#pragma unroll
-      for (int I = J + 1; I < WNT; ++I) {
-        const double2 a = Lf[32 * tri(I, K)];
-        dmma_xyt(acc[I], a, bj);
+        for (int I = J + 1; I < WNT; ++I) dmma_xyt(acc[I], Lf[32 * (tri(I, 0) + K)], bj);
       }
     }
-    const double2 li = wm_diag8(-acc[J].x, -acc[J].y);
+    const double2 li = wm_diag8(-acc[J].x, -acc[J].y, xb);
     bad = bad || !(li.x == li.x) || !(li.y == li.y);
-    Lf[32 * tri(J, J)] = tile_transpose(li, lane);
+    Lf[32 * tri(J, J)] = li;
     const double2 nli = make_double2(-li.x, -li.y);
 #pragma unroll
     for (int I = J + 1; I < WNT; ++I) {
@@ -195,70 +215,72 @@ __device__ __noinline__ bool wm_factor(const double* Hg, const double* wrow, int
       Lf[32 * tri(I, J)] = x;
     }
   }
-  return !__any_sync(0xffffffffu, bad);
+  const bool ok = !__any_sync(0xffffffffu, bad);
+  __syncwarp();  // the solves read tiles transposed, i.e. words written by other lanes
+  return ok;
 }
 
-// Solve L L' x = b in place on the 64-vector `x` in shared memory.  The caller must __syncwarp()
-// between writing b and this call, and again before reading x.
+// Solve L L' x = b in place on the 64-vector `x` in shared memory.  Right-looking block
+// substitution, everything in t-layout on the tensor pipe, straight-line code (72 tile products).
+// The caller must __syncwarp() between writing b and this call, and again before reading x.
 __device__ __noinline__ void wm_solve(const double* Ls, double* x) {
   const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   const double2* Lf = reinterpret_cast<const double2*>(Ls) + lane;
-  double yx[WNT], yy[WNT];
+  const double* Lt = Ls + 16 * t + g;  // transposed reads: {Lt[64 T], Lt[64 T + 8]} = {T[2t][g], T[2t+1][g]}
+  double2 r[WNT];
+#pragma unroll
+  for (int I = 0; I < WNT; ++I) r[I] = *reinterpret_cast<const double2*>(x + 8 * I + 2 * t);
   // forward: L y = b
 #pragma unroll
   for (int J = 0; J < WNT; ++J) {
-    const double bg = x[8 * J + g];
-    double p0 = 0.0, p1 = 0.0;
+    double2 y = make_double2(0.0, 0.0);
+    dmma_xyt(y, r[J], Lf[32 * tri(J, J)]);  // y_J = inv(L_JJ) r_J
+    r[J] = y;
+    const double2 ny = make_double2(-y.x, -y.y);
 #pragma unroll
-    for (int K = 0; K < J; ++K) {
-      const double2 l = Lf[32 * tri(J, K)];
-      p0 = fma(l.x, yx[K], p0);
-      p1 = fma(l.y, yy[K], p1);
-    }
-    const double r = bg - qsum(p0 + p1);            // g-layout
-    const double2 tt = Lf[32 * tri(J, J)];          // tt[g][j] = inv(L)[j][g]
-    yx[J] = gsum(tt.x * r);                         // y[2t]   = sum_g inv(L)[2t][g] r[g]
-    yy[J] = gsum(tt.y * r);
+    for (int I = J + 1; I < WNT; ++I) dmma_xyt(r[I], ny, Lf[32 * tri(I, J)]);  // r_I -= L_IJ y_J
   }
   // backward: L' x = y
-  double xg[WNT];
 #pragma unroll
   for (int J = WNT - 1; J >= 0; --J) {
-    double p0 = 0.0, p1 = 0.0;
+    double2 xx = make_double2(0.0, 0.0);
+    dmma_xyt(xx, r[J], make_double2(Lt[64 * tri(J, J)], Lt[64 * tri(J, J) + 8]));  // x_J = inv(L_JJ)' r_J
+    r[J] = xx;
+    const double2 nx = make_double2(-xx.x, -xx.y);
 #pragma unroll
-    for (int I = J + 1; I < WNT; ++I) {
-      const double2 l = Lf[32 * tri(I, J)];
-      p0 = fma(l.x, xg[I], p0);
-      p1 = fma(l.y, xg[I], p1);
-    }
-    double r0 = yx[J], r1 = yy[J];
-    if (J < WNT - 1) { r0 -= gsum(p0); r1 -= gsum(p1); }  // t-layout
-    const double2 tt = Lf[32 * tri(J, J)];                // x[g] = sum_j inv(L)'[g][j] r[j]
-    xg[J] = qsum(fma(tt.x, r0, tt.y * r1));
-    if (t == 0) x[8 * J + g] = xg[J];
+    for (int I = 0; I < J; ++I)
+      dmma_xyt(r[I], nx, make_double2(Lt[64 * tri(J, I)], Lt[64 * tri(J, I) + 8]));  // r_I -= L_JI' x_J
+  }
+  if (g == 0) {
+#pragma unroll
+    for (int I = 0; I < WNT; ++I) *reinterpret_cast<double2*>(x + 8 * I + 2 * t) = r[I];
   }
 }
 
 // y = H x for the full-symmetric fragment-ordered Hessian workspace (global, L2 resident);
-// x and y are 64-vectors in shared memory (x != y).  Caller syncs as for wm_solve.
-// Hg is written earlier in the same kernel: loads go through L2 (__ldcg).
+// x and y are 64-vectors in shared memory (x != y).  Caller syncs as for wm_solve.  Hg is
+// written earlier in the same kernel: loads go through L2 (__ldcg).
 __device__ __noinline__ void wm_symv(const double* Hg, const double* x, double* y) {
   const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   const double2* Hf = reinterpret_cast<const double2*>(Hg) + lane;
   double2 xt[WNT];
 #pragma unroll
   for (int J = 0; J < WNT; ++J) xt[J] = *reinterpret_cast<const double2*>(x + 8 * J + 2 * t);
-#pragma unroll
+#pragma unroll 1
   for (int I = 0; I < WNT; ++I) {
-    double p0 = 0.0, p1 = 0.0;
+    double2 a0 = make_double2(0.0, 0.0), a1 = a0, a2 = a0, a3 = a0;  // four independent DMMA chains
 #pragma unroll
-    for (int J = 0; J < WNT; ++J) {
-      const double2 h = __ldcg(Hf + 32 * (8 * I + J));
-      p0 = fma(h.x, xt[J].x, p0);
-      p1 = fma(h.y, xt[J].y, p1);
+    for (int J = 0; J < WNT; J += 2) {
+      const double2 h0 = __ldcg(Hf + 32 * (8 * I + J));
+      const double2 h1 = __ldcg(Hf + 32 * (8 * I + J + 1));
+      dmma(a0, xt[J].x, h0.x);
+      dmma(a1, xt[J].y, h0.y);
+      dmma(a2, xt[J + 1].x, h1.x);
+      dmma(a3, xt[J + 1].y, h1.y);
     }
-    const double s = qsum(p0 + p1);
-    if (t == 0) y[8 * I + g] = s;
+    if (g == 0)
+      *reinterpret_cast<double2*>(y + 8 * I + 2 * t) =
+          make_double2((a0.x + a1.x) + (a2.x + a3.x), (a0.y + a1.y) + (a2.y + a3.y));
   }
 }
 
