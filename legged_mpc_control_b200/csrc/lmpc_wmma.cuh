@@ -48,20 +48,29 @@ __device__ __forceinline__ int hfull_off(int r, int c) { return frag_off(((r >> 
 // factor storage: lower tiles only, tile (I, J), I >= J at index tri(I, J)
 __device__ __forceinline__ int lfac_off(int r, int c) { return frag_off(tri(r >> 3, c >> 3), r, c); }
 
-__device__ __noinline__ double wsum(double v) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-  return v;
+// c += A-slot a x B-slot b  (one k-chunk of an 8x8x4 FP64 tensor-core product)
+__device__ __forceinline__ void dmma(double2& c, double a, double b) {
+  asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+      : "+d"(c.x), "+d"(c.y)
+      : "d"(a), "d"(b));
 }
-__device__ __noinline__ double wmin(double v) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v = fmin(v, __shfl_xor_sync(0xffffffffu, v, o));
-  return v;
+// Sum over the warp on the tensor pipe: ones x v gives the quad sums (lane (g,t) holds those of
+// quads 2t, 2t+1), a second ones-product adds the eight quads.  Every lane gets the total.
+__device__ __forceinline__ double wsum(double v) {
+  double2 q = make_double2(0.0, 0.0);
+  dmma(q, 1.0, v);
+  double2 s = make_double2(0.0, 0.0);
+  dmma(s, 1.0, q.x + q.y);
+  return s.x;
 }
-__device__ __noinline__ double wmax(double v) {
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
-  return v;
+// Max over the warp of NON-NEGATIVE doubles (IEEE order == unsigned order of the bit pattern; a
+// NaN compares above everything and propagates): two 32-bit redux.sync steps.
+__device__ __forceinline__ double wmax(double v) {
+  v = fabs(v);  // callers pass non-negative values; this also folds -0.0
+  const unsigned hi = (unsigned)__double2hiint(v), lo = (unsigned)__double2loint(v);
+  const unsigned mh = __reduce_max_sync(0xffffffffu, hi);
+  const unsigned ml = __reduce_max_sync(0xffffffffu, hi == mh ? lo : 0u);
+  return __hiloint2double((int)mh, (int)ml);
 }
 // sum over the 4 lanes of a quad (over t)
 __device__ __forceinline__ double qsum(double v) {
@@ -96,27 +105,45 @@ __device__ __forceinline__ double frsqrt(double a) {
   return fma(0.5 * x, e, x);
 }
 
-// c += A-slot a x B-slot b  (one k-chunk of an 8x8x4 FP64 tensor-core product)
-__device__ __forceinline__ void dmma(double2& c, double a, double b) {
-  asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
-               : "+d"(c.x), "+d"(c.y)
-               : "d"(a), "d"(b));
-}
 // c += X * Y^T for two C-layout tiles (both k-chunks)
 __device__ __forceinline__ void dmma_xyt(double2& c, const double2& x, const double2& y) {
   dmma(c, x.x, y.x);
   dmma(c, x.y, y.y);
 }
+// Wider PTX shapes, same convention (fragment layouts verified on a B200 by tools/probe/mma_probe.cu).
+// NOT used on the hot path: ptxas lowers m16n8k8 / m16n8k16 to 4 / 8 DMMA.8x8x4 on sm_100a (the only
+// FP64 tensor SASS shape), so they save no issue slots; kept for reference.
+// [c1; c2] += [X1; X2] * Y^T (m16n8k8) ...
+__device__ __forceinline__ void dmma2_xyt(double2& c1, double2& c2, const double2& x1, const double2& x2,
+                                          const double2& y) {
+  asm("mma.sync.aligned.m16n8k8.row.col.f64.f64.f64.f64 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+d"(c1.x), "+d"(c1.y), "+d"(c2.x), "+d"(c2.y)
+      : "d"(x1.x), "d"(x2.x), "d"(x1.y), "d"(x2.y), "d"(y.x), "d"(y.y));
+}
+// ... and [c1; c2] += [X1a X1b; X2a X2b] * [Ya Yb]^T (two k-tiles) in ONE m16n8k16 instruction.
+__device__ __forceinline__ void dmma4_xyt(double2& c1, double2& c2, const double2& x1a, const double2& x2a,
+                                          const double2& x1b, const double2& x2b, const double2& ya,
+                                          const double2& yb) {
+  asm("mma.sync.aligned.m16n8k16.row.col.f64.f64.f64.f64 {%0,%1,%2,%3}, {%4,%5,%6,%7,%8,%9,%10,%11}, "
+      "{%12,%13,%14,%15}, {%0,%1,%2,%3};"
+      : "+d"(c1.x), "+d"(c1.y), "+d"(c2.x), "+d"(c2.y)
+      : "d"(x1a.x), "d"(x2a.x), "d"(x1a.y), "d"(x2a.y), "d"(x1b.x), "d"(x2b.x), "d"(x1b.y), "d"(x2b.y),
+        "d"(ya.x), "d"(ya.y), "d"(yb.x), "d"(yb.y));
+}
+// t-layout result of  sum over the quad of the lane-local partial dot products p  (see "vectors")
+__device__ __forceinline__ double2 quad_reduce_t(double p) {
+  double2 c = make_double2(0.0, 0.0);
+  dmma(c, 1.0, p);
+  return c;
+}
 
 
 // ---- vectors.  A 64-vector block v[8K..8K+7] lives in registers in "t-layout": lane (g, t) holds
-// the pair v[8K+2t], v[8K+2t+1], replicated over g.  That pair is directly the A operand of a
-// DMMA whose rows are all equal to v, so
-//   tile * v   = dmma_xyt(0, v, tile)           (tile read in C-layout, one LDS.128)
-//   tile' * v  = dmma_xyt(0, v, tile^T)         (tile read transposed, two LDS.64)
-// both return their result in t-layout again: triangular solves and H*x run on the tensor pipe
-// with no shuffle and no layout conversion (1/8 of the DMMA's MACs are useful, the FP64 pipe is
-// otherwise idle in those phases).
+// the pair v[8K+2t], v[8K+2t+1], replicated over g.  tile * v:  every lane multiplies its two tile
+// elements (row g, columns 2t, 2t+1) with its pair (two DFMAs, partials of several tiles
+// accumulate first), then ONE DMMA  ones x p  adds the four partials of each row AND returns the
+// result in t-layout (C[.][n] = sum_k p(lane (n,k))).  tile' * v works the same on a transposed
+// read (two LDS.64).  Triangular solves and H*x therefore need no shuffle and no layout change.
 
 // transposed read of a fragment-ordered tile: returns {T[2t][g], T[2t+1][g]}
 __device__ __forceinline__ double2 tile_ld_t(const double* tile, int g, int t) {
@@ -150,7 +177,9 @@ __device__ __noinline__ double2 wm_diag8(double ax, double ay, double* xb) {
     const double2 r = xs[o / 2];
     const double2 f = xs[o / 2 + 4];
     if (g == c) dg = d;
-    const double m = (g > c) ? acg * frcp(d) : 0.0;
+    const double rd_ = frcp(d);
+    double m = acg * rd_;
+    m = (g > c) ? m : 0.0;
     ax = fma(-m, r.x, ax); ay = fma(-m, r.y, ay);
     ex = fma(-m, f.x, ex); ey = fma(-m, f.y, ey);
   }
@@ -168,33 +197,44 @@ __device__ __noinline__ double2 wm_diag8(double ax, double ay, double* xb) {
 // the K loop rolled to keep the hot loop inside the instruction cache.
 // Returns false on a non-positive pivot.
 template <bool FROM_H>
+__device__ __forceinline__ double2 wm_load_m(const double2* Hf, const double2* Lf, const double* wrow, int n,
+                                             int I, int J, int g, int t) {
+  double2 v;
+  if (FROM_H) {
+    v = __ldcg(Hf + 32 * (8 * I + J));
+    if (I - J <= 1) {  // only these tiles can contain entries of a 3x3 pyramid block
+      const int r = 8 * I + g, c = 8 * J + 2 * t;
+      const int d0 = c - (r / 3) * 3;
+      if (r < n) {
+        if (d0 >= 0 && d0 < 3) v.x += wrow[3 * r + d0];
+        if (d0 >= -1 && d0 < 2) v.y += wrow[3 * r + d0 + 1];
+      }
+    }
+  } else {
+    v = Lf[32 * tri(I, J)];
+  }
+  return make_double2(-v.x, -v.y);
+}
+
+template <bool FROM_H>
 __device__ __noinline__ bool wm_factor(const double* Hg, const double* wrow, int n, double* Ls, double* xb) {
   const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   double2* Lf = reinterpret_cast<double2*>(Ls) + lane;
   const double2* Hf = reinterpret_cast<const double2*>(Hg) + lane;
   bool bad = false;
+  double2 nxt[WNT];  // column J+1 of M, fetched from L2 while column J is being eliminated
+#pragma unroll
+  for (int I = 0; I < WNT; ++I) nxt[I] = wm_load_m<FROM_H>(Hf, Lf, wrow, n, I, 0, g, t);
 #pragma unroll
   for (int J = 0; J < WNT; ++J) {
     double2 acc[WNT];
 #pragma unroll
-    for (int I = J; I < WNT; ++I) {
-      double2 v;
-      if (FROM_H) {
-        v = __ldcg(Hf + 32 * (8 * I + J));
-        if (I - J <= 1) {  // only these tiles can contain entries of a 3x3 pyramid block
-          const int r = 8 * I + g, c = 8 * J + 2 * t;
-          const int d0 = c - (r / 3) * 3;
-          if (r < n) {
-            if (d0 >= 0 && d0 < 3) v.x += wrow[3 * r + d0];
-            if (d0 >= -1 && d0 < 2) v.y += wrow[3 * r + d0 + 1];
-          }
-        }
-      } else {
-        v = Lf[32 * tri(I, J)];
-      }
-      acc[I] = make_double2(-v.x, -v.y);
+    for (int I = J; I < WNT; ++I) acc[I] = nxt[I];
+    if (J + 1 < WNT) {
+#pragma unroll
+      for (int I = J + 1; I < WNT; ++I) nxt[I] = wm_load_m<FROM_H>(Hf, Lf, wrow, n, I, J + 1, g, t);
     }
-    if (J > 0) {
+    if (J > 0) {  // acc[I] += L_IK L_JK' over K < J; the K loop stays rolled
       const double2* rowJ = Lf + 32 * tri(J, 0);
 #pragma unroll 1
       for (int K = 0; K < J; ++K) {
@@ -220,8 +260,9 @@ __device__ __noinline__ bool wm_factor(const double* Hg, const double* wrow, int
   return ok;
 }
 
-// Solve L L' x = b in place on the 64-vector `x` in shared memory.  Right-looking block
-// substitution, everything in t-layout on the tensor pipe, straight-line code (72 tile products).
+// Solve L L' x = b in place on the 64-vector `x` in shared memory.  Row-oriented block
+// substitution in t-layout: lane-local DFMA partials over the tiles of a block row, one ones-DMMA
+// per reduction (16 per triangular solve), straight-line code.
 // The caller must __syncwarp() between writing b and this call, and again before reading x.
 __device__ __noinline__ void wm_solve(const double* Ls, double* x) {
   const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
@@ -230,26 +271,37 @@ __device__ __noinline__ void wm_solve(const double* Ls, double* x) {
   double2 r[WNT];
 #pragma unroll
   for (int I = 0; I < WNT; ++I) r[I] = *reinterpret_cast<const double2*>(x + 8 * I + 2 * t);
-  // forward: L y = b
+  // forward: y_J = inv(L_JJ) (b_J - sum_{K<J} L_JK y_K)
 #pragma unroll
   for (int J = 0; J < WNT; ++J) {
-    double2 y = make_double2(0.0, 0.0);
-    dmma_xyt(y, r[J], Lf[32 * tri(J, J)]);  // y_J = inv(L_JJ) r_J
-    r[J] = y;
-    const double2 ny = make_double2(-y.x, -y.y);
+    if (J > 0) {
+      double p0 = 0.0, p1 = 0.0;
 #pragma unroll
-    for (int I = J + 1; I < WNT; ++I) dmma_xyt(r[I], ny, Lf[32 * tri(I, J)]);  // r_I -= L_IJ y_J
+      for (int K = 0; K < J; ++K) {
+        const double2 l = Lf[32 * tri(J, K)];
+        p0 = fma(l.x, r[K].x, p0);
+        p1 = fma(l.y, r[K].y, p1);
+      }
+      const double2 s = quad_reduce_t(p0 + p1);
+      r[J].x -= s.x; r[J].y -= s.y;
+    }
+    const double2 li = Lf[32 * tri(J, J)];
+    r[J] = quad_reduce_t(fma(li.x, r[J].x, li.y * r[J].y));
   }
-  // backward: L' x = y
+  // backward: x_J = inv(L_JJ)' (y_J - sum_{I>J} L_IJ' x_I)
 #pragma unroll
   for (int J = WNT - 1; J >= 0; --J) {
-    double2 xx = make_double2(0.0, 0.0);
-    dmma_xyt(xx, r[J], make_double2(Lt[64 * tri(J, J)], Lt[64 * tri(J, J) + 8]));  // x_J = inv(L_JJ)' r_J
-    r[J] = xx;
-    const double2 nx = make_double2(-xx.x, -xx.y);
+    if (J < WNT - 1) {
+      double p0 = 0.0, p1 = 0.0;
 #pragma unroll
-    for (int I = 0; I < J; ++I)
-      dmma_xyt(r[I], nx, make_double2(Lt[64 * tri(J, I)], Lt[64 * tri(J, I) + 8]));  // r_I -= L_JI' x_J
+      for (int I = J + 1; I < WNT; ++I) {
+        p0 = fma(Lt[64 * tri(I, J)], r[I].x, p0);
+        p1 = fma(Lt[64 * tri(I, J) + 8], r[I].y, p1);
+      }
+      const double2 s = quad_reduce_t(p0 + p1);
+      r[J].x -= s.x; r[J].y -= s.y;
+    }
+    r[J] = quad_reduce_t(fma(Lt[64 * tri(J, J)], r[J].x, Lt[64 * tri(J, J) + 8] * r[J].y));
   }
   if (g == 0) {
 #pragma unroll
@@ -266,21 +318,20 @@ __device__ __noinline__ void wm_symv(const double* Hg, const double* x, double* 
   double2 xt[WNT];
 #pragma unroll
   for (int J = 0; J < WNT; ++J) xt[J] = *reinterpret_cast<const double2*>(x + 8 * J + 2 * t);
-#pragma unroll 1
+#pragma unroll 2
   for (int I = 0; I < WNT; ++I) {
-    double2 a0 = make_double2(0.0, 0.0), a1 = a0, a2 = a0, a3 = a0;  // four independent DMMA chains
+    double p0 = 0.0, p1 = 0.0, p2 = 0.0, p3 = 0.0;
 #pragma unroll
     for (int J = 0; J < WNT; J += 2) {
       const double2 h0 = __ldcg(Hf + 32 * (8 * I + J));
       const double2 h1 = __ldcg(Hf + 32 * (8 * I + J + 1));
-      dmma(a0, xt[J].x, h0.x);
-      dmma(a1, xt[J].y, h0.y);
-      dmma(a2, xt[J + 1].x, h1.x);
-      dmma(a3, xt[J + 1].y, h1.y);
+      p0 = fma(h0.x, xt[J].x, p0);
+      p1 = fma(h0.y, xt[J].y, p1);
+      p2 = fma(h1.x, xt[J + 1].x, p2);
+      p3 = fma(h1.y, xt[J + 1].y, p3);
     }
-    if (g == 0)
-      *reinterpret_cast<double2*>(y + 8 * I + 2 * t) =
-          make_double2((a0.x + a1.x) + (a2.x + a3.x), (a0.y + a1.y) + (a2.y + a3.y));
+    const double2 s = quad_reduce_t((p0 + p1) + (p2 + p3));
+    if (g == 0) *reinterpret_cast<double2*>(y + 8 * I + 2 * t) = s;
   }
 }
 
