@@ -2,6 +2,7 @@
 // CPU path behind this ABI: every entry point that computes needs a CUDA device.
 #include <cuda_runtime.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <string>
@@ -192,6 +193,11 @@ static void fill_kparams(const lmpc_params& p, KParams* k) {
   k->dt = p.dt; k->mu = p.mu; k->fz_max = p.fz_max; k->mass = p.mass; k->gravity = p.gravity;
   k->cs = p.cost_scaling == LMPC_COST_NS_TWO ? 2.0 : 1.0;
   k->act_tol = p.active_tol > 0 ? p.active_tol : 1e-6;
+  // solver tuning (environment overrides are for experiments only)
+  k->tol0 = 1e-7; k->rdtol0 = 1e-9; k->fz0 = 0.0;
+  if (const char* e = getenv("LMPC_TOL0")) k->tol0 = atof(e);
+  if (const char* e = getenv("LMPC_RDTOL0")) k->rdtol0 = atof(e);
+  if (const char* e = getenv("LMPC_FZ0")) k->fz0 = atof(e);
   for (int i = 0; i < 9; ++i) k->inertia[i] = p.inertia[i];
   for (int i = 0; i < 12; ++i) { k->q[i] = p.q[i]; k->r[i] = p.r[i]; }
 }
@@ -326,6 +332,12 @@ static lmpc_status finish_solve(lmpc_handle* h, cudaStream_t s) {
   CK(cudaMemcpyAsync(&h->last_stats, h->d_stats.p, sizeof(KStats), cudaMemcpyDeviceToHost, s));
   CK(cudaStreamSynchronize(s));
   CK(cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1));
+  if (getenv("LMPC_DEBUG_STATS")) {
+    const KStats& k = h->last_stats;
+    const double np = k.problems ? (double)k.problems : 1.0;
+    fprintf(stderr, "[lmpc] problems %llu mean_n %.2f fact %.3f polish %.3f ipm_only %llu not_ok %llu kernel %.3f ms\n", k.problems,
+            k.sum_n / np, k.sum_fact / np, k.sum_polish / np, k.ipm_only, k.not_ok, h->last_ms);
+  }
   if (h->last_stats.not_ok > 0) {
     set_err(std::to_string((unsigned long long)h->last_stats.not_ok) + " problem(s) did not converge (grf zeroed)");
     return LMPC_ERR_NOT_CONVERGED;

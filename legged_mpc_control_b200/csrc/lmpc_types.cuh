@@ -13,6 +13,9 @@ struct KParams {
   double dt, mu, fz_max, mass, gravity;
   double cs;      // cost scaling (1: reference 1/2 z'Pz, 2: north-star)
   double act_tol; // primal activity tolerance [N]
+  double tol0;    // complementarity target of the first interior-point stage (then: exact polish)
+  double rdtol0;  // relative dual-residual target of the first stage
+  double fz0;     // initial fz as a fraction of fz_max (<= 0: m g / #stance legs of the step)
   double inertia[9];
   double q[12];
   double r[12];

@@ -261,6 +261,7 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
   // ---------------- stage 3: reduced Hessian into the L2 workspace (full symmetric 64x64)
   const double im2 = 1.0 / (mass * mass);
   double sc;
+  double hd[6] = {0, 0, 0, 0, 0, 0};  // own diagonal 3x3 block of the scaled Hessian: (0,0) (1,0) (2,0) (1,1) (2,1) (2,2)
   {
     double dmax = 0;
     if (lane < nb) {
@@ -268,9 +269,12 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
       const int j = blk[2 * lane], l = blk[2 * lane + 1];
       wblock(H, dt2, theta, P.cs, im2, qw, rw, Bw, cosv, sinv, Cs, Ss, j, l, j, l, true, o);
       dmax = fmax(fabs(o[0]), fmax(fabs(o[4]), fabs(o[8])));
+      hd[0] = o[0]; hd[1] = o[1]; hd[2] = o[2]; hd[3] = o[4]; hd[4] = o[5]; hd[5] = o[8];
     }
     dmax = wmax(dmax);
     sc = 1.0 / dmax;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) hd[k] *= sc;
     // identity padding for rows/cols >= n
     for (int idx = lane; idx < np * (np - n); idx += 32) {
       const int c = n + idx / np, r = idx % np;
@@ -308,32 +312,58 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
   __syncwarp();  // Hg visible to every lane; setup scratch (aliased with hu/rd/dua/du/wrow) is dead from here on
   double gsinf = wmax(fmax(fabs(gs[lane]), fabs(gs[lane + 32])));
   const double rd_tol = 1e-9 * (gsinf > 1.0 ? gsinf : 1.0);
+  const double rd_tol0 = P.rdtol0 * (gsinf > 1.0 ? gsinf : 1.0);
   const double dual_tol = 1e-9 * (gsinf > sc ? gsinf : sc);
   const double feas_tol = 1e-9;
   const int m = 5 * nb;
 
   // ---------------- stage 4a: interior point (feasible start)
-  // Lane b < nb owns stance block b: its force u_b, multipliers z_b and slacks stay in registers.
+  // Lane b < nb owns stance block b: its force u_b, multipliers z_b, slacks, gradient g_b and
+  // (H u)_b stay in registers.  The factorization reads M = H + C'WC from the L2 workspace: every
+  // iteration the owners overwrite their 3x3 diagonal block with H_bb + W_b (C'WC is block
+  // diagonal) and restore H_bb before the polish.  (H u)_b is updated from the Newton system,
+  // H du = rhs - C'WC du, and re-computed exactly (one H*x) only when convergence is claimed.
   // Ratio form of the step rules (q = ds/s):  -ds/s = -q,  -dz_aff/z = 1 + q,  so the predictor
   // needs no division; reciprocals come from frcp (rcp.approx + 2 Newton steps).
   const bool act = lane < nb;
   const double inv_m = 1.0 / (double)m;
-  double uf[3] = {0.0, 0.0, act ? 0.5 * fzm : 0.0};
+  double fz_init = P.fz0 * fzm;
+  if (P.fz0 <= 0.0 && act) {  // weight shared by the stance legs of this block's step
+    const uint8_t* ck = contact + 4 * blk[2 * lane];
+    const int ns = (ck[0] != 0) + (ck[1] != 0) + (ck[2] != 0) + (ck[3] != 0);
+    fz_init = fmin(0.9 * fzm, fmax(0.05 * fzm, mass * P.gravity / (double)ns));
+  }
+  double uf[3] = {0.0, 0.0, act ? fz_init : 0.0};
   double zr[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
+  double huf[3] = {0.0, 0.0, 0.0}, gsf[3] = {0.0, 0.0, 0.0};
+  int moff[9];  // workspace offsets of the own diagonal block, [a1 + 3 a2]
+#pragma unroll
+  for (int a1 = 0; a1 < 3; ++a1)
+#pragma unroll
+    for (int a2 = 0; a2 < 3; ++a2) moff[a1 + 3 * a2] = act ? hfull_off(3 * lane + a1, 3 * lane + a2) : 0;
   u[lane] = 0.0; u[lane + 32] = 0.0;
   hu[lane] = 0.0; hu[lane + 32] = 0.0;
+  dua[lane] = 0.0; dua[lane + 32] = 0.0;
+  du[lane] = 0.0; du[lane + 32] = 0.0;
   __syncwarp();
   if (act) u[3 * lane + 2] = uf[2];
-  for (int i = lane; i < 3 * WN; i += 32) wrow[i] = 0.0;
   __syncwarp();
   {
     wm_symv(Hg, u, hu);
     __syncwarp();
-    const double ginf = wmax(fmax(fabs(hu[lane] + gs[lane]), fabs(hu[lane + 32] + gs[lane + 32])));
-    double ssum = 0;
+    double ssum = 0, gi = 0;
     double s[5];
     blk_slack(uf, mu, fzm, s);
-    if (act) ssum = s[0] + s[1] + s[2] + s[3] + s[4];
+    if (act) {
+#pragma unroll
+      for (int a = 0; a < 3; ++a) {
+        huf[a] = hu[3 * lane + a];
+        gsf[a] = gs[3 * lane + a];
+        gi = fmax(gi, fabs(huf[a] + gsf[a]));
+      }
+      ssum = s[0] + s[1] + s[2] + s[3] + s[4];
+    }
+    const double ginf = wmax(gi);
     ssum = wsum(ssum);
     const double zc = (ginf > 1e-6 ? ginf : 1e-6) * (ssum * inv_m);
     if (act)
@@ -346,21 +376,20 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
   bool solved = false;
 #pragma unroll 1
   for (int stage = 0; stage < 3 && !solved; ++stage) {
-    const double mu_tol = stage == 0 ? 1e-7 : (stage == 1 ? 1e-10 : 1e-13);
+    const double mu_tol = stage == 0 ? P.tol0 : (stage == 1 ? 1e-10 : 1e-13);
+    const double rdt = stage == 0 ? rd_tol0 : rd_tol;
     bool ipm_converged = false, ipm_broken = false;
 #pragma unroll 1
     while (n_ipm < max_iter) {
-      wm_symv(Hg, u, hu);
-      __syncwarp();
-      double s[5], is[5], w[5], rdv[3] = {0.0, 0.0, 0.0};
+      double s[5], is[5], w[5], rdv[3] = {0.0, 0.0, 0.0}, ctz[3] = {0.0, 0.0, 0.0};
+      double wb[6] = {0, 0, 0, 0, 0, 0};  // C_b' W C_b: (0,0) (2,0) (1,1) (2,1) (2,2); (1,0) = 0
       double rdinf = 0, sz = 0;
       blk_slack(uf, mu, fzm, s);
       if (act) {
-        double ct[3];
-        blk_ct(zr, mu, ct);
+        blk_ct(zr, mu, ctz);
 #pragma unroll
         for (int a = 0; a < 3; ++a) {
-          rdv[a] = hu[3 * lane + a] + gs[3 * lane + a] + ct[a];
+          rdv[a] = huf[a] + gsf[a] + ctz[a];
           rdinf = fmax(rdinf, fabs(rdv[a]));
         }
 #pragma unroll
@@ -369,22 +398,53 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
           w[r] = zr[r] * is[r];
           sz = fma(s[r], zr[r], sz);
         }
-        double* wr = wrow + 9 * lane;  // rows 3b..3b+2 of C_b' W C_b, 3 entries each
-        wr[0] = w[0] + w[1]; wr[1] = 0.0; wr[2] = mu * (w[0] - w[1]);
-        wr[3] = 0.0; wr[4] = w[2] + w[3]; wr[5] = mu * (w[2] - w[3]);
-        wr[6] = wr[2]; wr[7] = wr[5]; wr[8] = mu * mu * (w[0] + w[1] + w[2] + w[3]) + w[4];
+        wb[0] = w[0] + w[1]; wb[1] = mu * (w[0] - w[1]);
+        wb[2] = w[2] + w[3]; wb[3] = mu * (w[2] - w[3]);
+        wb[4] = mu * mu * (w[0] + w[1] + w[2] + w[3]) + w[4];
       }
       rdinf = wmax(rdinf);
       sz = wsum(sz);
       const double mub = sz * inv_m;
       if (!(rdinf == rdinf) || !(mub == mub)) { ipm_broken = true; break; }
-      if (rdinf <= rd_tol && mub <= mu_tol) { ipm_converged = true; break; }
+      if (rdinf <= rdt && mub <= mu_tol) {
+        // convergence claimed on the recursively updated H u: confirm with an exact product on H
+        // itself (subtracting W u from M u would cancel catastrophically: W ~ z/s is huge here)
+        if (act) {
+          __stcg(Hg + moff[0], hd[0]); __stcg(Hg + moff[4], hd[3]); __stcg(Hg + moff[8], hd[5]);
+          __stcg(Hg + moff[1], hd[1]); __stcg(Hg + moff[3], hd[1]);
+          __stcg(Hg + moff[2], hd[2]); __stcg(Hg + moff[6], hd[2]);
+          __stcg(Hg + moff[5], hd[4]); __stcg(Hg + moff[7], hd[4]);
+        }
+        __syncwarp();
+        wm_symv(Hg, u, hu);
+        __syncwarp();
+        double ri = 0;
+        if (act) {
+#pragma unroll
+          for (int a = 0; a < 3; ++a) {
+            huf[a] = hu[3 * lane + a];
+            rdv[a] = huf[a] + gsf[a] + ctz[a];
+            ri = fmax(ri, fabs(rdv[a]));
+          }
+        }
+        rdinf = wmax(ri);
+        if (rdinf <= rdt) { ipm_converged = true; break; }
+      }
       ++n_ipm;
       // predictor: (H + C'WC) du_aff = -(H u + g)
-      dua[lane] = -(hu[lane] + gs[lane]); dua[lane + 32] = -(hu[lane + 32] + gs[lane + 32]);
-      du[lane] = 0.0; du[lane + 32] = 0.0;
+      if (act) {
+#pragma unroll
+        for (int a = 0; a < 3; ++a) dua[3 * lane + a] = -(huf[a] + gsf[a]);
+        // M_bb = H_bb + W_b into the workspace (both triangles; the block may straddle tiles)
+        __stcg(Hg + moff[0], hd[0] + wb[0]);
+        __stcg(Hg + moff[4], hd[3] + wb[2]);
+        __stcg(Hg + moff[8], hd[5] + wb[4]);
+        __stcg(Hg + moff[1], hd[1]); __stcg(Hg + moff[3], hd[1]);
+        __stcg(Hg + moff[2], hd[2] + wb[1]); __stcg(Hg + moff[6], hd[2] + wb[1]);
+        __stcg(Hg + moff[5], hd[4] + wb[3]); __stcg(Hg + moff[7], hd[4] + wb[3]);
+      }
       __syncwarp();
-      if (!wm_factor<true>(Hg, wrow, n, Ls, xb)) { ipm_broken = true; break; }
+      if (!wm_factor<true>(Hg, Ls, xb)) { ipm_broken = true; break; }
       wm_solve(Ls, dua);
       __syncwarp();
       double q[5], tau = 0.0;
@@ -408,14 +468,17 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
       const double rat = szaff * frcp(sz);
       const double smu = rat * rat * rat * mub;  // sigma * mu
       // corrector: rhs = -rd - C'((sigma mu - ds_aff dz_aff - s z)/s)
-      double w2[5];
+      double w2[5], rhs[3] = {0.0, 0.0, 0.0};
       if (act) {
         double ct[3];
 #pragma unroll
         for (int r = 0; r < 5; ++r) w2[r] = fma(zr[r], fma(q[r], 1.0 + q[r], -1.0), smu * is[r]);
         blk_ct(w2, mu, ct);
 #pragma unroll
-        for (int a = 0; a < 3; ++a) du[3 * lane + a] = -rdv[a] - ct[a];
+        for (int a = 0; a < 3; ++a) {
+          rhs[a] = -rdv[a] - ct[a];
+          du[3 * lane + a] = rhs[a];
+        }
       }
       __syncwarp();
       wm_solve(Ls, du);
@@ -437,13 +500,27 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
       if (act) {
 #pragma unroll
         for (int r = 0; r < 5; ++r) zr[r] = fma(alpha, dz[r], zr[r]);
+        // H du = rhs - W_b du  (Newton system), so H u follows without a matrix product
+        const double hd0 = rhs[0] - (wb[0] * duf[0] + wb[1] * duf[2]);
+        const double hd1 = rhs[1] - (wb[2] * duf[1] + wb[3] * duf[2]);
+        const double hd2 = rhs[2] - (wb[1] * duf[0] + wb[3] * duf[1] + wb[4] * duf[2]);
+        huf[0] = fma(alpha, hd0, huf[0]); huf[1] = fma(alpha, hd1, huf[1]); huf[2] = fma(alpha, hd2, huf[2]);
 #pragma unroll
-        for (int a = 0; a < 3; ++a) uf[a] = fma(alpha, duf[a], uf[a]);
+        for (int a = 0; a < 3; ++a) {
+          uf[a] = fma(alpha, duf[a], uf[a]);
+          u[3 * lane + a] = uf[a];
+        }
       }
-      u[lane] = fma(alpha, du[lane], u[lane]);
-      u[lane + 32] = fma(alpha, du[lane + 32], u[lane + 32]);
       __syncwarp();
     }
+    // the polish works on H itself: put the own diagonal block back
+    if (act) {
+      __stcg(Hg + moff[0], hd[0]); __stcg(Hg + moff[4], hd[3]); __stcg(Hg + moff[8], hd[5]);
+      __stcg(Hg + moff[1], hd[1]); __stcg(Hg + moff[3], hd[1]);
+      __stcg(Hg + moff[2], hd[2]); __stcg(Hg + moff[6], hd[2]);
+      __stcg(Hg + moff[5], hd[4]); __stcg(Hg + moff[7], hd[4]);
+    }
+    __syncwarp();
     if (ipm_broken) { status = 3; break; }
     if (stage == 2) {
       status = ipm_converged ? 1 : 2;
@@ -539,7 +616,7 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
         du[3 * b + 2] = (apex || top) ? 0.0 : -gzt;
       }
       __syncwarp();
-      if (!wm_factor<false>(Hg, wrow, n, Ls, xb)) break;
+      if (!wm_factor<false>(Hg, Ls, xb)) break;
       wm_solve(Ls, du);
       dua[lane] = 0.0; dua[lane + 32] = 0.0;
       __syncwarp();

@@ -161,7 +161,6 @@ __device__ __forceinline__ double2 tile_ld_t(const double* tile, int g, int t) {
 __device__ __noinline__ double2 wm_diag8(double ax, double ay, double* xb) {
   const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   double ex = (g == 2 * t) ? 1.0 : 0.0, ey = (g == 2 * t + 1) ? 1.0 : 0.0;
-  double dg = 1.0;
   double2* xs = reinterpret_cast<double2*>(xb) + t;   // this lane's column pair inside a row
   const double* xg = xb + g;
 #pragma unroll
@@ -172,76 +171,74 @@ __device__ __noinline__ double2 wm_diag8(double ax, double ay, double* xb) {
       xs[o / 2 + 4] = make_double2(ex, ey);
     }
     __syncwarp();
-    const double d = xb[o + c];
-    const double acg = xg[o];
+    const double rd_ = frcp(xb[o + c]);
+    double m = xg[o] * rd_;
     const double2 r = xs[o / 2];
     const double2 f = xs[o / 2 + 4];
-    if (g == c) dg = d;
-    const double rd_ = frcp(d);
-    double m = acg * rd_;
     m = (g > c) ? m : 0.0;
     ax = fma(-m, r.x, ax); ay = fma(-m, r.y, ay);
     ex = fma(-m, f.x, ex); ey = fma(-m, f.y, ey);
   }
-  const double d7 = __shfl_sync(0xffffffffu, ay, 31);  // last pivot A[7][7] lives in lane (7, 3)
-  if (g == 7) dg = d7;
+  // row g is final after step g-1, so its pivot d_g = A[g][g] sits in lane (g, g>>1): fetch it
+  const double dsel = (g & 1) ? ay : ax;
+  const double dg = __shfl_sync(0xffffffffu, dsel, (lane & 28) | (g >> 1));
   const double rs = (dg > 0.0) ? frsqrt(dg) : __longlong_as_double(0x7ff8000000000000ll);
   return make_double2(rs * ex, rs * ey);
 }
 
-// Factor M = L L' (64 x 64, 8 x 8 tiles).  FROM_H: M = Hg + blockdiag(W): Hg is the
-// full-symmetric fragment-ordered Hessian workspace in global memory (L2), W the 3x3 pyramid
-// blocks given row-wise in wrow[row][3] (rows >= n carry none).  !FROM_H: the lower tiles of M
-// are already in Ls (diagonal tiles full symmetric).  On exit Ls holds L_IJ (I > J) and inv(L_JJ)
-// in the diagonal slots.  Left-looking by tile columns: J unrolled (static accumulator indices),
-// the K loop rolled to keep the hot loop inside the instruction cache.
+// Factor M = L L' (64 x 64, 8 x 8 tiles).  FROM_G: the lower tiles of M are read from the
+// full-symmetric fragment-ordered workspace Mg in global memory (L2; the interior-point loop keeps
+// H + C'WC there), each tile column fetched one column ahead of its use.  !FROM_G: the lower tiles
+// of M are already in Ls (diagonal tiles full symmetric).  On exit Ls holds L_IJ (I > J) and
+// inv(L_JJ) in the diagonal slots.  Left-looking by tile columns: J unrolled (static accumulator
+// indices), the K loop rolled to keep the hot loop inside the instruction cache; for the narrow
+// late columns the two k-chunks of a tile product accumulate in separate chains.
 // Returns false on a non-positive pivot.
-template <bool FROM_H>
-__device__ __forceinline__ double2 wm_load_m(const double2* Hf, const double2* Lf, const double* wrow, int n,
-                                             int I, int J, int g, int t) {
-  double2 v;
-  if (FROM_H) {
-    v = __ldcg(Hf + 32 * (8 * I + J));
-    if (I - J <= 1) {  // only these tiles can contain entries of a 3x3 pyramid block
-      const int r = 8 * I + g, c = 8 * J + 2 * t;
-      const int d0 = c - (r / 3) * 3;
-      if (r < n) {
-        if (d0 >= 0 && d0 < 3) v.x += wrow[3 * r + d0];
-        if (d0 >= -1 && d0 < 2) v.y += wrow[3 * r + d0 + 1];
-      }
-    }
-  } else {
-    v = Lf[32 * tri(I, J)];
-  }
-  return make_double2(-v.x, -v.y);
-}
-
-template <bool FROM_H>
-__device__ __noinline__ bool wm_factor(const double* Hg, const double* wrow, int n, double* Ls, double* xb) {
-  const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+template <bool FROM_G>
+__device__ __noinline__ bool wm_factor(const double* Mg, double* Ls, double* xb) {
+  const int lane = threadIdx.x & 31;
   double2* Lf = reinterpret_cast<double2*>(Ls) + lane;
-  const double2* Hf = reinterpret_cast<const double2*>(Hg) + lane;
+  const double2* Mf = reinterpret_cast<const double2*>(Mg) + lane;
   bool bad = false;
-  double2 nxt[WNT];  // column J+1 of M, fetched from L2 while column J is being eliminated
+  double2 nxt[WNT];
 #pragma unroll
-  for (int I = 0; I < WNT; ++I) nxt[I] = wm_load_m<FROM_H>(Hf, Lf, wrow, n, I, 0, g, t);
+  for (int I = 0; I < WNT; ++I) nxt[I] = FROM_G ? __ldcg(Mf + 32 * (8 * I)) : Lf[32 * tri(I, 0)];
 #pragma unroll
   for (int J = 0; J < WNT; ++J) {
-    double2 acc[WNT];
+    double2 acc[WNT], acb[WNT];
 #pragma unroll
-    for (int I = J; I < WNT; ++I) acc[I] = nxt[I];
+    for (int I = J; I < WNT; ++I) {
+      acc[I] = make_double2(-nxt[I].x, -nxt[I].y);
+      acb[I] = make_double2(0.0, 0.0);
+    }
     if (J + 1 < WNT) {
 #pragma unroll
-      for (int I = J + 1; I < WNT; ++I) nxt[I] = wm_load_m<FROM_H>(Hf, Lf, wrow, n, I, J + 1, g, t);
+      for (int I = J + 1; I < WNT; ++I)
+        nxt[I] = FROM_G ? __ldcg(Mf + 32 * (8 * I + J + 1)) : Lf[32 * tri(I, J + 1)];
     }
-    if (J > 0) {  // acc[I] += L_IK L_JK' over K < J; the K loop stays rolled
+    if (J > 0) {  // acc[I] += L_IK L_JK' over K < J
       const double2* rowJ = Lf + 32 * tri(J, 0);
 #pragma unroll 1
       for (int K = 0; K < J; ++K) {
         const double2 bj = rowJ[32 * K];
-        dmma_xyt(acc[J], bj, bj);
+        if (J >= 4) {
+          dmma(acc[J], bj.x, bj.x);
+          dmma(acb[J], bj.y, bj.y);
 #pragma unroll
-        for (int I = J + 1; I < WNT; ++I) dmma_xyt(acc[I], Lf[32 * (tri(I, 0) + K)], bj);
+          for (int I = J + 1; I < WNT; ++I) {
+            const double2 a = Lf[32 * (tri(I, 0) + K)];
+            dmma(acc[I], a.x, bj.x);
+            dmma(acb[I], a.y, bj.y);
+          }
+        } else {
+          dmma_xyt(acc[J], bj, bj);
+#pragma unroll
+          for (int I = J + 1; I < WNT; ++I) dmma_xyt(acc[I], Lf[32 * (tri(I, 0) + K)], bj);
+        }
+      }
+      if (J >= 4) {
+#pragma unroll
+        for (int I = J; I < WNT; ++I) { acc[I].x += acb[I].x; acc[I].y += acb[I].y; }
       }
     }
     const double2 li = wm_diag8(-acc[J].x, -acc[J].y, xb);

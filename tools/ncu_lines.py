@@ -21,10 +21,15 @@ def sass_lines(so, kernel_sub):
     out = []
     for f in sorted(os.listdir(d)):
         txt = subprocess.run(["nvdisasm", "-g", os.path.join(d, f)], capture_output=True, text=True).stdout
-        cur, inside = None, False
+        cur, inside, fn = None, False, None
         for ln in txt.splitlines():
             if ln.startswith(".text."):
                 inside = kernel_sub in ln
+                fn = None
+                continue
+            mf = re.match(r"\$[^$]+\$(\S+):\s*$", ln)
+            if mf and inside:
+                fn = mf.group(1)
                 continue
             if ln.lstrip().startswith(".section"):
                 inside = False
@@ -36,7 +41,7 @@ def sass_lines(so, kernel_sub):
                 continue
             m = re.match(r"\s*/\*([0-9a-f]{4,})\*/\s+(.*?);", ln)
             if m:
-                out.append((int(m.group(1), 16), cur, m.group(2).strip()))
+                out.append((int(m.group(1), 16), cur, m.group(2).strip(), fn))
         if out:
             break
     return out
@@ -76,6 +81,29 @@ def main():
     for loc, e in inst.most_common(top):
         o = ", ".join(f"{a}:{100*b/max(e,1):.0f}%" for a, b in ops[loc].most_common(4))
         print(f"{(loc[0]+':'+str(loc[1])) if loc else '?':38s} {100*e/ti:7.2f} {100*samp[loc]/max(ts,1):7.2f}  {o}")
+    # by code region: kernel body vs called device functions (CALL targets), body split by the
+    # enclosing source line of the kernel's main file (carried forward over inlined helpers)
+    reg_i, reg_s = collections.Counter(), collections.Counter()
+    _dm = {}
+    main_file = os.environ.get("NCU_LINES_MAIN", "lmpc_warp_solve.cuh")
+    bucket = int(os.environ.get("NCU_LINES_BUCKET", "50"))
+    cur = 0
+    for k in range(n):
+        addr, loc = sl[k][0], sl[k][1]
+        e = int(body[k][ci["Instructions Executed"]] or 0)
+        sm = int(body[k][ci["# Samples"]] or 0)
+        if sl[k][3] is None:
+            if loc and loc[0] == main_file:
+                cur = (loc[1] // bucket) * bucket
+            key = f"body {main_file}:{cur}-{cur + bucket - 1}"
+        else:
+            key = "func " + subprocess.run(["c++filt", sl[k][3]], capture_output=True, text=True).stdout.strip()[:60] if sl[k][3] not in _dm else _dm[sl[k][3]]
+            _dm[sl[k][3]] = key
+        reg_i[key] += e
+        reg_s[key] += sm
+    print("by region:")
+    for key, e in reg_i.most_common(30):
+        print(f"  {key:44s} inst {100*e/ti:6.2f}%  samples {100*reg_s[key]/max(ts,1):6.2f}%")
     # opcode totals
     tot = collections.Counter()
     for loc in ops:
