@@ -163,7 +163,7 @@ __device__ __noinline__ double2 wm_diag8(double ax, double ay, double* xb) {
   double ex = (g == 2 * t) ? 1.0 : 0.0, ey = (g == 2 * t + 1) ? 1.0 : 0.0;
   double2* xs = reinterpret_cast<double2*>(xb) + t;   // this lane's column pair inside a row
   const double* xg = xb + g;
-#pragma unroll
+#pragma unroll 1
   for (int c = 0; c < 7; ++c) {
     const int o = 16 * (c & 1);
     if (g == c) {
