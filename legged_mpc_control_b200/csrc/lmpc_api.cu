@@ -11,18 +11,28 @@
 #include "../../include/lmpc.h"
 #include "lmpc_solver.cuh"
 #include "lmpc_warp_solve.cuh"
+#include "lmpc_tile_solve.cuh"
 
 namespace lmpc {
 
 // ---------------------------------------------------------------- kernels
 
-// Reduced dimension of every problem (3 per stance leg-step) -> size class.  Class A (n <= 63:
-// the one-warp-per-QP path) and class B (everything larger: the CTA-per-QP path) are compacted
-// into two index lists with warp-aggregated atomics; n_max of class B sizes its shared memory.
-// counts[0] = |A|, counts[1] = |B|.
+// Size classes by reduced dimension n (3 per stance leg-step):
+//   0: n <= 63            one warp per QP, 8 x 8 tiles        (solve_warp_kernel)
+//   1: 64 <= n <= 120     one warp per QP, 15 x 15 tiles      (solve_tile_kernel<15>)
+//   2: 121 <= n <= 192    one warp per QP, 24 x 24 tiles      (solve_tile_kernel<24>)
+//   3: n > 192            one CTA per QP, packed matrices     (solve_kernel)
+constexpr int kNumClasses = 4;
+constexpr int kTileA = 15, kTileB = 24;
+__host__ __device__ inline int size_class(int n) {
+  return n <= 3 * WNBMAX ? 0 : (n <= 8 * kTileA ? 1 : (n <= 8 * kTileB ? 2 : 3));
+}
+
+// Compacts the problems of every size class into its own index list (order + cls * B) with
+// warp-aggregated atomics; counts[cls] = size of the class; n_max of class 3 sizes its shared memory.
 __global__ void classify_kernel(const uint8_t* __restrict__ contact, int H, int B,
-                                KStats* __restrict__ stats, int* __restrict__ orderA,
-                                int* __restrict__ orderB, int* __restrict__ counts) {
+                                KStats* __restrict__ stats, int* __restrict__ order, int stride,
+                                int* __restrict__ counts) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int lane = threadIdx.x & 31;
   int n = -1;
@@ -31,23 +41,56 @@ __global__ void classify_kernel(const uint8_t* __restrict__ contact, int H, int 
     n = 0;
     for (int t = 0; t < 4 * H; ++t) n += c[t] ? 3 : 0;
   }
-  const bool isA = n >= 0 && n <= 3 * WNBMAX;
-  const bool isB = n > 3 * WNBMAX;
-  const unsigned mA = __ballot_sync(0xffffffffu, isA), mB = __ballot_sync(0xffffffffu, isB);
-  int baseA = 0, baseB = 0;
-  if (lane == 0) {
-    if (mA) baseA = atomicAdd(&counts[0], __popc(mA));
-    if (mB) baseB = atomicAdd(&counts[1], __popc(mB));
-  }
-  baseA = __shfl_sync(0xffffffffu, baseA, 0);
-  baseB = __shfl_sync(0xffffffffu, baseB, 0);
+  const int cls = n >= 0 ? size_class(n) : -1;
   const unsigned lt = (1u << lane) - 1u;
-  if (isA) orderA[baseA + __popc(mA & lt)] = i;
-  if (isB) orderB[baseB + __popc(mB & lt)] = i;
-  int nB = isB ? n : 0;
+#pragma unroll
+  for (int k = 0; k < kNumClasses; ++k) {
+    const unsigned m = __ballot_sync(0xffffffffu, cls == k);
+    int base = 0;
+    if (lane == 0 && m) base = atomicAdd(&counts[k], __popc(m));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (cls == k) order[(size_t)k * stride + base + __popc(m & lt)] = i;
+  }
+  int nB = cls == 3 ? n : 0;
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) nB = max(nB, __shfl_xor_sync(0xffffffffu, nB, o));
   if (lane == 0 && nB > 0) atomicMax(&stats->n_max, nB);
+}
+
+__device__ inline void flush_warp_stats(const WarpStats& ws, KStats* stats) {
+  if ((threadIdx.x & 31) == 0 && ws.problems) {
+    atomicAdd(&stats->problems, ws.problems);
+    atomicAdd(&stats->sum_n, ws.sum_n);
+    atomicAdd(&stats->sum_fact, ws.sum_fact);
+    atomicAdd(&stats->sum_polish, ws.sum_polish);
+    if (ws.not_ok) atomicAdd(&stats->not_ok, ws.not_ok);
+    if (ws.ipm_only) atomicAdd(&stats->ipm_only, ws.ipm_only);
+    atomicAdd(&stats->flops, ws.flops);
+  }
+}
+
+// Persistent one-warp-per-QP solve for 64 <= n <= 8 NT: fragment-ordered factor in shared memory
+// (61 KB at NT = 15: three warps per SM; 154 KB at NT = 24: one), Hessian slot in the L2 workspace.
+template <int NT>
+__global__ void __launch_bounds__(32) solve_tile_kernel(const __grid_constant__ KParams P,
+                                                        const __grid_constant__ KBatch Bt, KStats* stats,
+                                                        double* gws, const int* __restrict__ count,
+                                                        int* work_counter) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const TilePlan pl = make_tile_plan<NT>(P.H);
+  constexpr size_t kSlot = (size_t)TileGeom<NT>::HS + 6 * TileGeom<NT>::NBMAX + 2;
+  double* Hg = gws + (size_t)blockIdx.x * kSlot;
+  const int lane = threadIdx.x;
+  const int total = *count;
+  WarpStats ws;
+  for (;;) {
+    int w = 0;
+    if (lane == 0) w = atomicAdd(work_counter, 1);
+    w = __shfl_sync(0xffffffffu, w, 0);
+    if (w >= total) break;
+    solve_one_tile<NT>(P, Bt, ws, pl, smem, Hg, Bt.order[w]);
+  }
+  flush_warp_stats(ws, stats);
 }
 
 // Persistent one-warp-per-QP solve (class A).  One warp per CTA: no block barrier exists in this
@@ -71,15 +114,7 @@ __global__ void __launch_bounds__(32, 9) solve_warp_kernel(const __grid_constant
     if (w >= total) break;
     solve_one_warp(P, Bt, ws, pl, smem, Hg, Bt.order[w]);
   }
-  if (lane == 0 && ws.problems) {
-    atomicAdd(&stats->problems, ws.problems);
-    atomicAdd(&stats->sum_n, ws.sum_n);
-    atomicAdd(&stats->sum_fact, ws.sum_fact);
-    atomicAdd(&stats->sum_polish, ws.sum_polish);
-    if (ws.not_ok) atomicAdd(&stats->not_ok, ws.not_ok);
-    if (ws.ipm_only) atomicAdd(&stats->ipm_only, ws.ipm_only);
-    atomicAdd(&stats->flops, ws.flops);
-  }
+  flush_warp_stats(ws, stats);
 }
 
 // Persistent solve: one CTA per QP at a time, problems handed out by an atomic counter.
@@ -160,7 +195,7 @@ struct lmpc_handle {
   // device staging for host-pointer calls
   DevBuf d_x0, d_rot, d_foot, d_cmd, d_contact, d_q, d_r, d_mu, d_fz, d_mass, d_inertia;
   DevBuf d_grf, d_status, d_iters, d_active, d_U;
-  DevBuf d_stats, d_counter, d_ws, d_wsA, d_order;
+  DevBuf d_stats, d_counter, d_ws, d_wsA, d_wsT1, d_wsT2, d_order;
   cudaEvent_t ev_cls = nullptr;
   int* h_cls = nullptr;  // pinned: n_max, |A|, |B|
   KStats last_stats;
@@ -236,8 +271,8 @@ extern "C" lmpc_status lmpc_create(const lmpc_params* params, int32_t max_batch,
   CK(cudaEventCreateWithFlags(&h->ev_cls, cudaEventDisableTiming));
   CK(cudaMallocHost((void**)&h->h_cls, 4 * sizeof(int)));
   CK(h->d_stats.ensure(sizeof(KStats)));
-  CK(h->d_counter.ensure(4 * sizeof(int)));  // work counters A, B ; counts A, B
-  CK(h->d_order.ensure(2 * (size_t)max_batch * sizeof(int)));
+  CK(h->d_counter.ensure(8 * sizeof(int)));  // work counters [4], class sizes [4]
+  CK(h->d_order.ensure(4 * (size_t)max_batch * sizeof(int)));
   memset(&h->last_stats, 0, sizeof(KStats));
   *out = h;
   return LMPC_OK;
@@ -249,7 +284,7 @@ extern "C" void lmpc_destroy(lmpc_handle* h) {
   if (h->stream) cudaStreamSynchronize(h->stream);
   DevBuf* bufs[] = {&h->d_x0, &h->d_rot, &h->d_foot, &h->d_cmd, &h->d_contact, &h->d_q, &h->d_r, &h->d_mu,
                     &h->d_fz, &h->d_mass, &h->d_inertia, &h->d_grf, &h->d_status, &h->d_iters, &h->d_active,
-                    &h->d_U, &h->d_stats, &h->d_counter, &h->d_ws, &h->d_wsA, &h->d_order};
+                    &h->d_U, &h->d_stats, &h->d_counter, &h->d_ws, &h->d_wsA, &h->d_wsT1, &h->d_wsT2, &h->d_order};
   for (DevBuf* b : bufs) b->release();
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
@@ -259,24 +294,49 @@ extern "C" void lmpc_destroy(lmpc_handle* h) {
   delete h;
 }
 
-// Launch classify + the two size-class solves on `s` for the device-resident batch `kb`.
-// The class-A (one warp per QP) kernel is enqueued right behind the classification; the host
-// only waits for the 12-byte read-back that sizes the class-B launch, while class A runs.
+template <int NT>
+static lmpc_status launch_tile(lmpc_handle* h, const KBatch& kb, cudaStream_t s, DevBuf* wsbuf, int* order, int* count,
+                               int* work) {
+  const lmpc::TilePlan tp = lmpc::make_tile_plan<NT>(h->kp.H);
+  auto kern = lmpc::solve_tile_kernel<NT>;
+  CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tp.total_bytes));
+  int occ = 0;
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 32, tp.total_bytes));
+  if (occ < 1) { set_err("tile solve kernel does not fit on an SM"); return LMPC_ERR_CUDA; }
+  int grid = h->num_sms * occ;
+  if (grid > kb.B) grid = kb.B;
+  const size_t slot = (size_t)lmpc::TileGeom<NT>::HS + 6 * lmpc::TileGeom<NT>::NBMAX + 2;
+  CK(wsbuf->ensure((size_t)grid * slot * sizeof(double)));
+  KBatch k = kb;
+  k.order = order;
+  kern<<<grid, 32, tp.total_bytes, s>>>(h->kp, k, (KStats*)h->d_stats.p, (double*)wsbuf->p, count, work);
+  h->launches++;
+  CK(cudaGetLastError());
+  return LMPC_OK;
+}
+
+// Launch classify + the per-size-class solves on `s` for the device-resident batch `kb`.  The
+// one-warp-per-QP kernels are enqueued right behind the classification (they read their class
+// size on the device); the host only waits for the 16-byte read-back that sizes the CTA-per-QP
+// launch of the largest class, while the others run.
 static lmpc_status launch_solve(lmpc_handle* h, KBatch kb, cudaStream_t s) {
   const int H = h->kp.H;
   KStats* dstats = (KStats*)h->d_stats.p;
-  int* ctr = (int*)h->d_counter.p;       // [0] work A, [1] work B, [2] |A|, [3] |B|
-  int* orderA = (int*)h->d_order.p;
-  int* orderB = orderA + h->max_batch;
+  int* ctr = (int*)h->d_counter.p;  // [0..3] work counters, [4..7] class sizes
+  int* order = (int*)h->d_order.p;  // class c at order + c * max_batch
+  const int stride = h->max_batch;
   CK(cudaMemsetAsync(dstats, 0, sizeof(KStats), s));
-  CK(cudaMemsetAsync(ctr, 0, 4 * sizeof(int), s));
+  CK(cudaMemsetAsync(ctr, 0, 8 * sizeof(int), s));
   CK(cudaEventRecord(h->ev0, s));
-  lmpc::classify_kernel<<<(kb.B + 255) / 256, 256, 0, s>>>(kb.contact, H, kb.B, dstats, orderA, orderB, ctr + 2);
+  lmpc::classify_kernel<<<(kb.B + 255) / 256, 256, 0, s>>>(kb.contact, H, kb.B, dstats, order, stride, ctr + 4);
   h->launches++;
-  CK(cudaMemcpyAsync(h->h_cls, &dstats->n_max, sizeof(int), cudaMemcpyDeviceToHost, s));
-  CK(cudaMemcpyAsync(h->h_cls + 1, ctr + 2, 2 * sizeof(int), cudaMemcpyDeviceToHost, s));
-  CK(cudaEventRecord(h->ev_cls, s));
-  // ---- class A: one warp per QP
+  const bool may3 = 12 * H > 8 * lmpc::kTileB;
+  if (may3) {
+    CK(cudaMemcpyAsync(h->h_cls, &dstats->n_max, sizeof(int), cudaMemcpyDeviceToHost, s));
+    CK(cudaMemcpyAsync(h->h_cls + 1, ctr + 7, sizeof(int), cudaMemcpyDeviceToHost, s));
+    CK(cudaEventRecord(h->ev_cls, s));
+  }
+  // ---- class 0: one warp per QP, 8 x 8 tiles
   {
     const lmpc::WarpPlan wp = lmpc::make_warp_plan(H);
     auto kernA = lmpc::solve_warp_kernel;
@@ -288,41 +348,52 @@ static lmpc_status launch_solve(lmpc_handle* h, KBatch kb, cudaStream_t s) {
     if (grid > kb.B) grid = kb.B;
     CK(h->d_wsA.ensure((size_t)grid * lmpc::WN * lmpc::WN * sizeof(double)));
     KBatch ka = kb;
-    ka.order = orderA;
-    kernA<<<grid, 32, wp.total_bytes, s>>>(h->kp, ka, dstats, (double*)h->d_wsA.p, ctr + 2, ctr + 0);
+    ka.order = order;
+    kernA<<<grid, 32, wp.total_bytes, s>>>(h->kp, ka, dstats, (double*)h->d_wsA.p, ctr + 4, ctr + 0);
     h->launches++;
     CK(cudaGetLastError());
   }
-  CK(cudaEventSynchronize(h->ev_cls));
-  const int n_max = h->h_cls[0], countB = h->h_cls[2];
-  if (countB > 0) {
-    // ---- class B: one CTA per QP; choose where the two packed matrices live
-    int ncap = n_max > 0 ? n_max : 3;
-    lmpc::SmemPlan pl = lmpc::make_plan(H, ncap, true);
-    int in_smem = 1;
-    if (pl.total_bytes > h->smem_optin) {
-      in_smem = 0;
-      pl = lmpc::make_plan(H, ncap, false);
-      if (pl.total_bytes > h->smem_optin) { set_err("shared-memory plan does not fit even with spilled matrices"); return LMPC_ERR_INVALID_ARG; }
+  // ---- classes 1, 2: one warp per QP, 15 x 15 / 24 x 24 tiles (only if the horizon can reach them)
+  if (12 * H > 3 * lmpc::WNBMAX) {
+    lmpc_status st = launch_tile<lmpc::kTileA>(h, kb, s, &h->d_wsT1, order + stride, ctr + 5, ctr + 1);
+    if (st != LMPC_OK) return st;
+  }
+  if (12 * H > 8 * lmpc::kTileA) {
+    lmpc_status st = launch_tile<lmpc::kTileB>(h, kb, s, &h->d_wsT2, order + 2 * (size_t)stride, ctr + 6, ctr + 2);
+    if (st != LMPC_OK) return st;
+  }
+  if (may3) {
+    CK(cudaEventSynchronize(h->ev_cls));
+    const int n_max = h->h_cls[0], countB = h->h_cls[1];
+    if (countB > 0) {
+      // ---- class 3: one CTA per QP; choose where the two packed matrices live
+      int ncap = n_max > 0 ? n_max : 3;
+      lmpc::SmemPlan pl = lmpc::make_plan(H, ncap, true);
+      int in_smem = 1;
+      if (pl.total_bytes > h->smem_optin) {
+        in_smem = 0;
+        pl = lmpc::make_plan(H, ncap, false);
+        if (pl.total_bytes > h->smem_optin) { set_err("shared-memory plan does not fit even with spilled matrices"); return LMPC_ERR_INVALID_ARG; }
+      }
+      auto kern = lmpc::solve_kernel<kThreads>;
+      CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total_bytes));
+      int occ = 0;
+      CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kThreads, pl.total_bytes));
+      if (occ < 1) { set_err("solve kernel does not fit on an SM"); return LMPC_ERR_CUDA; }
+      int grid = h->num_sms * occ;
+      if (grid > countB) grid = countB;
+      double* gws = nullptr;
+      if (!in_smem) {
+        size_t bytes = (size_t)grid * 2 * lmpc::packed_size(ncap) * sizeof(double);
+        CK(h->d_ws.ensure(bytes));
+        gws = (double*)h->d_ws.p;
+      }
+      KBatch kbB = kb;
+      kbB.order = order + 3 * (size_t)stride;
+      kern<<<grid, kThreads, pl.total_bytes, s>>>(h->kp, kbB, dstats, ncap, in_smem, gws, ctr + 7, ctr + 3);
+      h->launches++;
+      CK(cudaGetLastError());
     }
-    auto kern = lmpc::solve_kernel<kThreads>;
-    CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total_bytes));
-    int occ = 0;
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kThreads, pl.total_bytes));
-    if (occ < 1) { set_err("solve kernel does not fit on an SM"); return LMPC_ERR_CUDA; }
-    int grid = h->num_sms * occ;
-    if (grid > countB) grid = countB;
-    double* gws = nullptr;
-    if (!in_smem) {
-      size_t bytes = (size_t)grid * 2 * lmpc::packed_size(ncap) * sizeof(double);
-      CK(h->d_ws.ensure(bytes));
-      gws = (double*)h->d_ws.p;
-    }
-    KBatch kbB = kb;
-    kbB.order = orderB;
-    kern<<<grid, kThreads, pl.total_bytes, s>>>(h->kp, kbB, dstats, ncap, in_smem, gws, ctr + 3, ctr + 1);
-    h->launches++;
-    CK(cudaGetLastError());
   }
   CK(cudaEventRecord(h->ev1, s));
   return LMPC_OK;

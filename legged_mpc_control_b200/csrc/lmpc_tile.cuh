@@ -1,0 +1,153 @@
+// lmpc_tile.cuh — dense FP64 kernels of the one-warp-per-QP path for ANY tile count NT (padded
+// dimension 8 NT; used for 64 <= n <= 192, i.e. H = 20 / H = 30 schedules).  Same fragment-ordered
+// 8x8 tiles, DMMA trailing updates and t-layout vectors as lmpc_wmma.cuh (read its header first),
+// but with loops rolled over the tile column J: the accumulators are indexed RELATIVE to the
+// column (acc[i] is tile row J + i), so one copy of the code serves every column and the kernel
+// stays small however large NT is.
+//
+// Factor storage: lower tiles, COLUMN-major packed, tile (I, K) (I >= K) at index
+//   lcol(K) + (I - K),   lcol(K) = K NT - K (K - 1) / 2,
+// so the tiles of one column are contiguous (immediate address offsets in the unrolled i loops).
+// The Hessian workspace in global memory (L2) is full symmetric, tile (I, J) at index I NT + J.
+#pragma once
+#include "lmpc_wmma.cuh"
+
+namespace lmpc {
+
+template <int NT>
+struct TileGeom {
+  static constexpr int N = 8 * NT;                   // padded dimension
+  static constexpr int LTILES = NT * (NT + 1) / 2;   // tiles of the factor
+  static constexpr int LS = LTILES * 64;             // doubles of factor storage
+  static constexpr int HS = NT * NT * 64;            // doubles of the Hessian workspace
+  static constexpr int NBMAX = (8 * NT) / 3;         // stance blocks that fit
+  __host__ __device__ static constexpr int lcol(int K) { return K * NT - (K * (K - 1)) / 2; }
+  // element offsets (in doubles)
+  __device__ static __forceinline__ int hoff(int r, int c) { return frag_off((r >> 3) * NT + (c >> 3), r, c); }
+  __device__ static __forceinline__ int loff(int r, int c) { return frag_off(lcol(c >> 3) + (r >> 3) - (c >> 3), r, c); }
+};
+
+// Factor M = L L' on NT x NT tiles.  FROM_G: lower tiles of M read from the workspace Mg (L2);
+// !FROM_G: M's lower tiles are already in Ls (diagonal tiles full symmetric).  On exit Ls holds
+// L_IJ (I > J) and inv(L_JJ) in the diagonal slots.  Returns false on a non-positive pivot.
+template <int NT, bool FROM_G>
+__device__ __noinline__ bool gm_factor(const double* Mg, double* Ls, double* xb) {
+  using G = TileGeom<NT>;
+  const int lane = threadIdx.x & 31;
+  double2* Lf = reinterpret_cast<double2*>(Ls) + lane;
+  const double2* Mf = reinterpret_cast<const double2*>(Mg) + lane;
+  bool bad = false;
+#pragma unroll 1
+  for (int J = 0; J < NT; ++J) {
+    const int cnt = NT - J;
+    double2* colL = Lf + 32 * G::lcol(J);              // tile (J + i, J) at colL[32 i]
+    const double2* colM = Mf + 32 * (J * NT + J);      // tile (J + i, J) at colM[32 NT i]
+    double2 acc[NT];
+#pragma unroll
+    for (int i = 0; i < NT; ++i) {
+      if (i < cnt) {
+        const double2 v = FROM_G ? __ldcg(colM + 32 * NT * i) : colL[32 * i];
+        acc[i] = make_double2(-v.x, -v.y);
+      }
+    }
+#pragma unroll 1
+    for (int K = 0; K < J; ++K) {  // acc[i] += L_{J+i,K} L_{J,K}'
+      const double2* p = Lf + 32 * (G::lcol(K) + J - K);
+      const double2 bj = p[0];
+      dmma_xyt(acc[0], bj, bj);
+#pragma unroll
+      for (int i = 1; i < NT; ++i) {
+        if (i < cnt) dmma_xyt(acc[i], p[32 * i], bj);
+      }
+    }
+    const double2 li = wm_diag8(-acc[0].x, -acc[0].y, xb);
+    bad = bad || !(li.x == li.x) || !(li.y == li.y);
+    colL[0] = li;
+    const double2 nli = make_double2(-li.x, -li.y);
+#pragma unroll
+    for (int i = 1; i < NT; ++i) {
+      if (i < cnt) {
+        double2 x = make_double2(0.0, 0.0);
+        dmma_xyt(x, acc[i], nli);
+        colL[32 * i] = x;
+      }
+    }
+  }
+  const bool ok = !__any_sync(0xffffffffu, bad);
+  __syncwarp();
+  return ok;
+}
+
+// Solve L L' x = b in place on the (8 NT)-vector x in shared memory.  Row-oriented block
+// substitution in t-layout; the solved blocks are read back from x itself (every lane re-reads the
+// pair it wrote, so no barrier is needed inside).  Caller syncs before and after.
+template <int NT>
+__device__ __noinline__ void gm_solve(const double* Ls, double* x) {
+  using G = TileGeom<NT>;
+  const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const double2* Lf = reinterpret_cast<const double2*>(Ls) + lane;
+  double2* xt = reinterpret_cast<double2*>(x) + t;  // block K pair at xt[4 K]
+  // forward: y_J = inv(L_JJ) (b_J - sum_{K<J} L_JK y_K)
+#pragma unroll 1
+  for (int J = 0; J < NT; ++J) {
+    double p0 = 0.0, p1 = 0.0;
+    const double2* p = Lf + 32 * J;  // tile (J, 0); tile (J, K+1) is NT - K - 1 tiles further
+#pragma unroll 4
+    for (int K = 0; K < J; ++K) {
+      const double2 l = *p;
+      const double2 y = xt[4 * K];
+      p0 = fma(l.x, y.x, p0);
+      p1 = fma(l.y, y.y, p1);
+      p += 32 * (NT - K - 1);
+    }
+    double2 r = xt[4 * J];
+    if (J > 0) {
+      const double2 s = quad_reduce_t(p0 + p1);
+      r.x -= s.x; r.y -= s.y;
+    }
+    const double2 li = Lf[32 * G::lcol(J)];
+    xt[4 * J] = quad_reduce_t(fma(li.x, r.x, li.y * r.y));
+  }
+  // backward: x_J = inv(L_JJ)' (y_J - sum_{I>J} L_IJ' x_I)
+#pragma unroll 1
+  for (int J = NT - 1; J >= 0; --J) {
+    const double* ct = Ls + 64 * G::lcol(J) + 16 * t + g;  // transposed reads of column J: tile i at ct[64 i], ct[64 i + 8]
+    double p0 = 0.0, p1 = 0.0;
+#pragma unroll 4
+    for (int i = 1; i < NT - J; ++i) {
+      const double2 xi = xt[4 * (J + i)];
+      p0 = fma(ct[64 * i], xi.x, p0);
+      p1 = fma(ct[64 * i + 8], xi.y, p1);
+    }
+    double2 r = xt[4 * J];
+    if (J < NT - 1) {
+      const double2 s = quad_reduce_t(p0 + p1);
+      r.x -= s.x; r.y -= s.y;
+    }
+    xt[4 * J] = quad_reduce_t(fma(ct[0], r.x, ct[8] * r.y));
+  }
+}
+
+// y = H x for the full-symmetric workspace (global, L2); x, y (8 NT)-vectors in shared memory.
+template <int NT>
+__device__ __noinline__ void gm_symv(const double* Hg, const double* x, double* y) {
+  const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const double2* Hf = reinterpret_cast<const double2*>(Hg) + lane;
+  const double2* xt = reinterpret_cast<const double2*>(x) + t;
+#pragma unroll 1
+  for (int I = 0; I < NT; ++I) {
+    double p0 = 0.0, p1 = 0.0;
+    const double2* row = Hf + 32 * (I * NT);
+#pragma unroll 8
+    for (int J = 0; J < NT; ++J) {
+      const double2 h = __ldcg(row + 32 * J);
+      const double2 v = xt[4 * J];
+      p0 = fma(h.x, v.x, p0);
+      p1 = fma(h.y, v.y, p1);
+    }
+    const double2 s = quad_reduce_t(p0 + p1);
+    if (g == 0) *reinterpret_cast<double2*>(y + 8 * I + 2 * t) = s;
+  }
+}
+
+}  // namespace lmpc

@@ -11,7 +11,10 @@ B = int(sys.argv[1]) if len(sys.argv) > 1 else 8192
 name = sys.argv[2] if len(sys.argv) > 2 else "northstar_a1"
 reps = int(sys.argv[3]) if len(sys.argv) > 3 else 3
 p = presets.preset(name)
-b = synth.make_batch(B, p.horizon, p.dt, seed=3, robot="go1" if "go1" in name else "a1")
+from legged_mpc_control_b200 import abi
+go1 = "go1" in name
+b = synth.make_batch(B, p.horizon, p.dt, seed=2 if go1 else 3, robot="go1" if go1 else "a1",
+                     gaits=(abi.GAIT_TROT, abi.GAIT_BOUND, abi.GAIT_PRONK) if go1 else (abi.GAIT_TROT,))
 dev = torch.device("cuda:0")
 tin = {k: torch.from_numpy(b[k]).to(dev) for k in ("x0", "rot", "foot_pos_abs", "cmd", "contact")}
 grf = torch.zeros(B, 12, dtype=torch.float64, device=dev)
