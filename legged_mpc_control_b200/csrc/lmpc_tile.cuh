@@ -1,9 +1,8 @@
 // lmpc_tile.cuh — dense FP64 kernels of the one-warp-per-QP path for ANY tile count NT (padded
 // dimension 8 NT; used for 64 <= n <= 192, i.e. H = 20 / H = 30 schedules).  Same fragment-ordered
 // 8x8 tiles, DMMA trailing updates and t-layout vectors as lmpc_wmma.cuh (read its header first),
-// but with loops rolled over the tile column J: the accumulators are indexed RELATIVE to the
-// column (acc[i] is tile row J + i), so one copy of the code serves every column and the kernel
-// stays small however large NT is.
+// with the triangular solves and H*x rolled over the tile index (vectors stay in shared memory)
+// and the factorization unrolled over the tile column only (static accumulator indices).
 //
 // Factor storage: lower tiles, COLUMN-major packed, tile (I, K) (I >= K) at index
 //   lcol(K) + (I - K),   lcol(K) = K NT - K (K - 1) / 2,
@@ -27,52 +26,63 @@ struct TileGeom {
   __device__ static __forceinline__ int loff(int r, int c) { return frag_off(lcol(c >> 3) + (r >> 3) - (c >> 3), r, c); }
 };
 
+// One tile column of the factorization with a compile-time tile count CNT = NT - J (static
+// accumulator indices, no predicated tensor instructions); the K loop stays rolled.
+template <int NT, int CNT, bool FROM_G>
+__device__ __forceinline__ bool gm_column(const double2* Mf, double2* Lf, double* xb) {
+  using G = TileGeom<NT>;
+  constexpr int J = NT - CNT;
+  double2* colL = Lf + 32 * G::lcol(J);              // tile (J + i, J) at colL[32 i]
+  const double2* colM = Mf + 32 * (J * NT + J);      // tile (J + i, J) at colM[32 NT i]
+  double2 acc[CNT];
+#pragma unroll
+  for (int i = 0; i < CNT; ++i) {
+    const double2 v = FROM_G ? __ldcg(colM + 32 * NT * i) : colL[32 * i];
+    acc[i] = make_double2(-v.x, -v.y);
+  }
+  if (J > 0) {
+    const double2* p = Lf + 32 * J;  // tile (J, 0); column K + 1 starts NT - K - 1 tiles further
+#pragma unroll 1
+    for (int K = 0; K < J; ++K) {  // acc[i] += L_{J+i,K} L_{J,K}'
+      const double2 bj = p[0];
+      dmma_xyt(acc[0], bj, bj);
+#pragma unroll
+      for (int i = 1; i < CNT; ++i) dmma_xyt(acc[i], p[32 * i], bj);
+      p += 32 * (NT - K - 1);
+    }
+  }
+  const double2 li = wm_diag8u(-acc[0].x, -acc[0].y, xb);
+  colL[0] = li;
+  const double2 nli = make_double2(-li.x, -li.y);
+#pragma unroll
+  for (int i = 1; i < CNT; ++i) {
+    double2 x = make_double2(0.0, 0.0);
+    dmma_xyt(x, acc[i], nli);
+    colL[32 * i] = x;
+  }
+  return !(li.x == li.x) || !(li.y == li.y);
+}
+template <int NT, int CNT, bool FROM_G>
+struct GmColumns {
+  __device__ static __forceinline__ bool run(const double2* Mf, double2* Lf, double* xb) {
+    const bool b = gm_column<NT, CNT, FROM_G>(Mf, Lf, xb);
+    return GmColumns<NT, CNT - 1, FROM_G>::run(Mf, Lf, xb) || b;
+  }
+};
+template <int NT, bool FROM_G>
+struct GmColumns<NT, 0, FROM_G> {
+  __device__ static __forceinline__ bool run(const double2*, double2*, double*) { return false; }
+};
+
 // Factor M = L L' on NT x NT tiles.  FROM_G: lower tiles of M read from the workspace Mg (L2);
 // !FROM_G: M's lower tiles are already in Ls (diagonal tiles full symmetric).  On exit Ls holds
 // L_IJ (I > J) and inv(L_JJ) in the diagonal slots.  Returns false on a non-positive pivot.
 template <int NT, bool FROM_G>
 __device__ __noinline__ bool gm_factor(const double* Mg, double* Ls, double* xb) {
-  using G = TileGeom<NT>;
   const int lane = threadIdx.x & 31;
   double2* Lf = reinterpret_cast<double2*>(Ls) + lane;
   const double2* Mf = reinterpret_cast<const double2*>(Mg) + lane;
-  bool bad = false;
-#pragma unroll 1
-  for (int J = 0; J < NT; ++J) {
-    const int cnt = NT - J;
-    double2* colL = Lf + 32 * G::lcol(J);              // tile (J + i, J) at colL[32 i]
-    const double2* colM = Mf + 32 * (J * NT + J);      // tile (J + i, J) at colM[32 NT i]
-    double2 acc[NT];
-#pragma unroll
-    for (int i = 0; i < NT; ++i) {
-      if (i < cnt) {
-        const double2 v = FROM_G ? __ldcg(colM + 32 * NT * i) : colL[32 * i];
-        acc[i] = make_double2(-v.x, -v.y);
-      }
-    }
-#pragma unroll 1
-    for (int K = 0; K < J; ++K) {  // acc[i] += L_{J+i,K} L_{J,K}'
-      const double2* p = Lf + 32 * (G::lcol(K) + J - K);
-      const double2 bj = p[0];
-      dmma_xyt(acc[0], bj, bj);
-#pragma unroll
-      for (int i = 1; i < NT; ++i) {
-        if (i < cnt) dmma_xyt(acc[i], p[32 * i], bj);
-      }
-    }
-    const double2 li = wm_diag8(-acc[0].x, -acc[0].y, xb);
-    bad = bad || !(li.x == li.x) || !(li.y == li.y);
-    colL[0] = li;
-    const double2 nli = make_double2(-li.x, -li.y);
-#pragma unroll
-    for (int i = 1; i < NT; ++i) {
-      if (i < cnt) {
-        double2 x = make_double2(0.0, 0.0);
-        dmma_xyt(x, acc[i], nli);
-        colL[32 * i] = x;
-      }
-    }
-  }
+  const bool bad = GmColumns<NT, NT, FROM_G>::run(Mf, Lf, xb);
   const bool ok = !__any_sync(0xffffffffu, bad);
   __syncwarp();
   return ok;

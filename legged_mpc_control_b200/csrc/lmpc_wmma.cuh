@@ -186,6 +186,35 @@ __device__ __noinline__ double2 wm_diag8(double ax, double ay, double* xb) {
   return make_double2(rs * ex, rs * ey);
 }
 
+// Same, fully unrolled (used where few warps share an SM and the instruction cache is no concern).
+__device__ __noinline__ double2 wm_diag8u(double ax, double ay, double* xb) {
+  const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  double ex = (g == 2 * t) ? 1.0 : 0.0, ey = (g == 2 * t + 1) ? 1.0 : 0.0;
+  double2* xs = reinterpret_cast<double2*>(xb) + t;   // this lane's column pair inside a row
+  const double* xg = xb + g;
+#pragma unroll
+  for (int c = 0; c < 7; ++c) {
+    const int o = 16 * (c & 1);
+    if (g == c) {
+      xs[o / 2] = make_double2(ax, ay);
+      xs[o / 2 + 4] = make_double2(ex, ey);
+    }
+    __syncwarp();
+    const double rd_ = frcp(xb[o + c]);
+    double m = xg[o] * rd_;
+    const double2 r = xs[o / 2];
+    const double2 f = xs[o / 2 + 4];
+    m = (g > c) ? m : 0.0;
+    ax = fma(-m, r.x, ax); ay = fma(-m, r.y, ay);
+    ex = fma(-m, f.x, ex); ey = fma(-m, f.y, ey);
+  }
+  // row g is final after step g-1, so its pivot d_g = A[g][g] sits in lane (g, g>>1): fetch it
+  const double dsel = (g & 1) ? ay : ax;
+  const double dg = __shfl_sync(0xffffffffu, dsel, (lane & 28) | (g >> 1));
+  const double rs = (dg > 0.0) ? frsqrt(dg) : __longlong_as_double(0x7ff8000000000000ll);
+  return make_double2(rs * ex, rs * ey);
+}
+
 // Factor M = L L' (64 x 64, 8 x 8 tiles).  FROM_G: the lower tiles of M are read from the
 // full-symmetric fragment-ordered workspace Mg in global memory (L2; the interior-point loop keeps
 // H + C'WC there), each tile column fetched one column ahead of its use.  !FROM_G: the lower tiles
