@@ -214,6 +214,38 @@ def run_b200(args):
     sampler.stop_flag = True
     sampler.join(timeout=2)
 
+    # ---- warm-started re-solves (OSQP warm-start analogue): alternate between the batch and a
+    #      slightly moved copy, so every solve starts from the faces of a near but different problem
+    warm_info = None
+    if not args.no_warm:
+        x0b = tin["x0"] + 1e-3 * torch.randn(tin["x0"].shape, dtype=torch.float64, device=dev,
+                                             generator=torch.Generator(device=dev).manual_seed(1234 + rank))
+        pin_b = dict(pin)
+        pin_b["x0"] = x0b.data_ptr()
+        eng.set_warm_start(True, horizon_shift=0)
+        eng.solve_device(pin, pout, B, stream=stream, wait=True)
+        wev, hits, wfact = [], 0, 0.0
+        with torch.cuda.stream(ts):
+            for i in range(args.steps):
+                flush.fill_(i)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(ts)
+                eng.solve_device(pin_b if i % 2 == 0 else pin, pout, B, stream=stream, wait=True)
+                e1.record(ts)
+                wev.append((e0, e1))
+                hits += eng.last_warm_hits
+                wfact += eng.last_stats()["mean_factorizations"]
+        barrier()
+        wms = sum(a.elapsed_time(b) for a, b in wev)
+        tw = torch.tensor([wms], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tw, op=dist.ReduceOp.MAX)
+        warm_info = {"value": world * B * args.steps / (float(tw.item()) * 1e-3), "unit": UNIT,
+                     "warm_hit_fraction": hits / (B * args.steps), "mean_factorizations": wfact / args.steps,
+                     "bad_status": int((tout["status"] > 1).sum().item()),
+                     "what": "same workload, every solve warm-started from the stored faces of a copy of the batch moved by 1e-3 in x0"}
+        eng.set_warm_start(False)
+
     # ---- final result gather (the only exchange the path has; outside the timed region)
     if world > 1:
         from legged_mpc_control_b200 import shard
@@ -259,9 +291,67 @@ def run_b200(args):
             },
             "cpu_baseline": {"value": cpu_val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
             "not_converged": bad,
+            "warm_start": warm_info,
         }
         print(json.dumps(line), flush=True)
     eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_rollout(args):
+    """BASELINE config 5: closed-loop batched SRBD rollout, `--robots` robots per GPU x
+    `--rollout-steps` control steps, warm-started QPs, state resident on the device (lmpc_rollout).
+    One line per run: robot-steps/s (= MPC solves/s in closed loop) and per-step p50 for cold and warm."""
+    import torch
+    import torch.distributed as dist
+    from legged_mpc_control_b200.engine import ConvexMpcEngine
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    p = presets.preset(PRESET)
+    B, S = args.robots, args.rollout_steps
+    res = {}
+    for mode, warm in (("cold", 0), ("warm", 1)):
+        st = synth.make_rollout_state(B, seed=5, start=rank * B)
+        fr = st.pop("foot_rel")
+        t = {k: torch.from_numpy(v).to(dev) for k, v in st.items()}
+        ptrs = {k: v.data_ptr() for k, v in t.items()}
+        ptrs["batch"] = B
+        eng = ConvexMpcEngine(p, B, device=local)
+        eng.rollout(dict(ptrs), 20, fr, warm_start=warm, on_device=True)  # warm-up (state advances 20 steps)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        chunk, ms, out_tot = 50, [], {"solves": 0, "factorizations": 0, "warm_hits": 0, "not_converged": 0}
+        n0 = eng.launch_count
+        for c in range(0, S, chunk):
+            o = eng.rollout(dict(ptrs), min(chunk, S - c), fr, warm_start=2 if warm else 0, on_device=True)
+            ms.append(o["device_ms"] / min(chunk, S - c))
+            for k in out_tot:
+                out_tot[k] += o[k]
+        total_ms = sum(m * min(chunk, S - c) for m, c in zip(ms, range(0, S, chunk)))
+        tt = torch.tensor([total_ms], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        x = t["x"].cpu().numpy()
+        res[mode] = {"robot_steps_per_s": world * B * S / (float(tt.item()) * 1e-3), "p50_step_ms": float(np.median(ms)),
+                     "mean_factorizations": out_tot["factorizations"] / max(1, out_tot["solves"]),
+                     "warm_hit_fraction": out_tot["warm_hits"] / max(1, out_tot["solves"]),
+                     "not_converged": out_tot["not_converged"], "launches": eng.launch_count - n0,
+                     "final_height_err_max": float(np.abs(x[:, 5] - st["cmd"][:, 2]).max()),
+                     "final_tilt_max": float(np.abs(x[:, 0:2]).max())}
+        eng.close()
+    if rank == 0:
+        print(json.dumps({"metric": "closed_loop_robot_steps_per_sec", "unit": "robot-steps/s", "value": res["warm"]["robot_steps_per_s"],
+                          "n_gpus": world, "higher_is_better": True, "scaling": "weak", "dtype": "f64", "data": "synthetic",
+                          "config": {"workload": f"config5_rollout_{B}robots_x_{S}steps_a1_trot_h{p.horizon}_dt{p.dt}", "preset": PRESET,
+                                     "robots_per_gpu": B, "steps": S}, "cold": res["cold"], "warm": res["warm"]}), flush=True)
     if world > 1:
         dist.destroy_process_group()
 
@@ -281,11 +371,18 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=BATCH)
+    ap.add_argument("--no-warm", action="store_true", help="skip the warm-started re-solve measurement")
+    ap.add_argument("--workload", default="headline", choices=["headline", "rollout"],
+                    help="rollout: BASELINE config 5 (16384 robots x --rollout-steps control steps, closed loop on device)")
+    ap.add_argument("--rollout-steps", type=int, default=1000)
+    ap.add_argument("--robots", type=int, default=16384)
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = 3  # timing rule: W >= 3
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload == "rollout":
+        run_rollout(args)
     else:
         run_b200(args)
 

@@ -165,8 +165,21 @@ lmpc_status lmpc_solve_async(lmpc_handle* h, int32_t batch, const lmpc_batch_in*
                              const lmpc_batch_out* out, void* cuda_stream);
 lmpc_status lmpc_wait(lmpc_handle* h);
 
-/* Forget the device-resident warm start (OSQP warm start analogue, ConvexQPSolver.cpp:185). */
+/* Warm start (OSQP `setWarmStart(true)` analogue, ConvexQPSolver.cpp:185).  When enabled, every
+ * solve stores the pyramid face of each stance block of problem i (device resident, 4H+4 bytes per
+ * problem) and the next solve of problem i first tries the exact active-set solve on those faces,
+ * shifted `horizon_shift` steps along the horizon (1 when the controller runs once per MPC step, as
+ * the reference does: MPC_UPDATE_FREQUENCY == dt, LeggedParams.h:7, ConvexQPSolver.cpp:26).  A guess
+ * that does not pass the on-device KKT check falls back to the cold interior-point path, so the
+ * result is the same exact minimiser either way.  Problem identity is the batch index.  Disabled by
+ * default. */
+lmpc_status lmpc_set_warm_start(lmpc_handle* h, int32_t enable, int32_t horizon_shift);
+
+/* Forget the device-resident warm start (e.g. after a robot reset). */
 lmpc_status lmpc_reset_warm_start(lmpc_handle* h);
+
+/* Problems of the last solve that were solved from the stored faces alone. */
+int64_t lmpc_last_warm_hits(const lmpc_handle* h);
 
 void lmpc_destroy(lmpc_handle* h);
 
@@ -207,6 +220,47 @@ int32_t lmpc_gait_predict_contact(int32_t gait, int32_t leg, double phase, doubl
 lmpc_status lmpc_gait_contact_table(int32_t batch, int32_t horizon, double dt, const int32_t* gait,
                                     const double* phase, const double* gait_speed,
                                     uint8_t* contact);
+
+/* ---- closed-loop batched rollout (BASELINE config 5): headless replacement of the loop the
+ * reference closes through Gazebo.  Per control step and robot, all on the device: contact table
+ * from the gait phase (LeggedContactFSM::predict_contact_state via ConvexQPSolver.cpp:329-346),
+ * Raibert footholds for swing legs (src/interfaces/BaseInterface.cpp:358-399), the MPC solve of
+ * lmpc_solve (warm-started), then x+ = A_d x + B_d u - g dt e_vz with the solver's own
+ * discretisation (ConvexQPSolver.cpp:198-228) and the phase advance (LeggedContactFSM.cpp:50).
+ * The control period is params.dt (the reference runs the MPC once per MPC step). ---- */
+typedef struct lmpc_rollout_state { /* one record per robot; all host or all device pointers */
+  double* x;                /* [B][12] in/out  euler, pos, omega, vel (ConvexQPSolver.cpp:256-259) */
+  double* foot_world;       /* [B][12] in/out  foot positions in the world frame, 3x4 col-major */
+  double* phase;            /* [B][4]  in/out  per-leg gait phase in [0,1] (LeggedContactFSM gait_phase) */
+  const int32_t* gait;      /* [B]     LMPC_GAIT_* */
+  const double* gait_speed; /* [B]     gait_counter_speed [1/s] (config yaml :19) */
+  const double* cmd;        /* [B][9]  as lmpc_batch_in.cmd */
+  int32_t on_device;
+  int32_t reserved0;
+} lmpc_rollout_state;
+
+typedef struct lmpc_rollout_cfg {
+  int32_t steps;
+  int32_t warm_start;              /* 0 cold every tick; 1 warm, faces reset first; 2 warm, keep faces of the previous call */
+  double default_foot_pos_rel[12]; /* param.default_foot_pos_rel 3x4 col-major (config yaml :21-32) */
+  double foot_delta_x_limit;       /* 0 -> FOOT_DELTA_X_LIMIT 0.8 (LeggedParams.h:29) */
+  double foot_delta_y_limit;       /* 0 -> FOOT_DELTA_Y_LIMIT 0.8 (LeggedParams.h:30) */
+  double ground_z;                 /* world height at which swing feet land (flat terrain) */
+} lmpc_rollout_cfg;
+
+typedef struct lmpc_rollout_result {
+  double* grf;     /* optional [B][12]: GRFs of the last step (same memory kind as the state) */
+  double* x_log;   /* optional [steps][B][12]: state after every step */
+  double* grf_log; /* optional [steps][B][12]: GRFs applied in every step */
+  int64_t solves, factorizations, polish_rounds, not_converged, warm_hits;
+  double flops_executed;
+  double mean_n_eff;
+  float device_ms; /* CUDA-event time of the whole loop on the handle's stream */
+  int32_t reserved0;
+} lmpc_rollout_result;
+
+lmpc_status lmpc_rollout(lmpc_handle* h, int32_t batch, const lmpc_rollout_cfg* cfg,
+                         const lmpc_rollout_state* state, lmpc_rollout_result* result);
 
 #ifdef __cplusplus
 }

@@ -13,7 +13,8 @@ EXPORTS = (
     "lmpc_params_preset", "lmpc_create", "lmpc_solve", "lmpc_solve_async", "lmpc_wait",
     "lmpc_reset_warm_start", "lmpc_destroy", "lmpc_last_error_string", "lmpc_abi_version",
     "lmpc_launch_count", "lmpc_last_kernel_ms", "lmpc_last_stats", "lmpc_gait_predict_contact",
-    "lmpc_gait_contact_table", "lmpc_microbench_fp64",
+    "lmpc_gait_contact_table", "lmpc_microbench_fp64", "lmpc_set_warm_start", "lmpc_last_warm_hits",
+    "lmpc_rollout",
 )
 
 
@@ -42,6 +43,11 @@ def lib():
     L.lmpc_solve_async.argtypes = [C.c_void_p, C.c_int32, C.POINTER(abi.LmpcBatchIn), C.POINTER(abi.LmpcBatchOut), C.c_void_p]
     L.lmpc_wait.argtypes = [C.c_void_p]
     L.lmpc_reset_warm_start.argtypes = [C.c_void_p]
+    L.lmpc_set_warm_start.argtypes = [C.c_void_p, C.c_int32, C.c_int32]
+    L.lmpc_last_warm_hits.argtypes = [C.c_void_p]
+    L.lmpc_last_warm_hits.restype = C.c_int64
+    L.lmpc_rollout.argtypes = [C.c_void_p, C.c_int32, C.POINTER(abi.LmpcRolloutCfg), C.POINTER(abi.LmpcRolloutState),
+                               C.POINTER(abi.LmpcRolloutResult)]
     L.lmpc_destroy.argtypes = [C.c_void_p]
     L.lmpc_destroy.restype = None
     L.lmpc_last_stats.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)]

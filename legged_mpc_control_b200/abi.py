@@ -82,6 +82,47 @@ class LmpcBatchOut(C.Structure):
     ]
 
 
+class LmpcRolloutState(C.Structure):
+    _fields_ = [
+        ("x", C.c_void_p),
+        ("foot_world", C.c_void_p),
+        ("phase", C.c_void_p),
+        ("gait", C.c_void_p),
+        ("gait_speed", C.c_void_p),
+        ("cmd", C.c_void_p),
+        ("on_device", C.c_int32),
+        ("reserved0", C.c_int32),
+    ]
+
+
+class LmpcRolloutCfg(C.Structure):
+    _fields_ = [
+        ("steps", C.c_int32),
+        ("warm_start", C.c_int32),
+        ("default_foot_pos_rel", C.c_double * 12),
+        ("foot_delta_x_limit", C.c_double),
+        ("foot_delta_y_limit", C.c_double),
+        ("ground_z", C.c_double),
+    ]
+
+
+class LmpcRolloutResult(C.Structure):
+    _fields_ = [
+        ("grf", C.c_void_p),
+        ("x_log", C.c_void_p),
+        ("grf_log", C.c_void_p),
+        ("solves", C.c_int64),
+        ("factorizations", C.c_int64),
+        ("polish_rounds", C.c_int64),
+        ("not_converged", C.c_int64),
+        ("warm_hits", C.c_int64),
+        ("flops_executed", C.c_double),
+        ("mean_n_eff", C.c_double),
+        ("device_ms", C.c_float),
+        ("reserved0", C.c_int32),
+    ]
+
+
 IN_FIELDS = (
     # name, per-problem elements (None -> 4*H), dtype, required
     ("x0", 12, np.float64, True),

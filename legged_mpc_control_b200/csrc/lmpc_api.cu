@@ -12,6 +12,7 @@
 #include "lmpc_solver.cuh"
 #include "lmpc_warp_solve.cuh"
 #include "lmpc_tile_solve.cuh"
+#include "lmpc_rollout.cuh"
 
 namespace lmpc {
 
@@ -65,6 +66,7 @@ __device__ inline void flush_warp_stats(const WarpStats& ws, KStats* stats) {
     atomicAdd(&stats->sum_polish, ws.sum_polish);
     if (ws.not_ok) atomicAdd(&stats->not_ok, ws.not_ok);
     if (ws.ipm_only) atomicAdd(&stats->ipm_only, ws.ipm_only);
+    if (ws.warm_hits) atomicAdd(&stats->warm_hits, ws.warm_hits);
     atomicAdd(&stats->flops, ws.flops);
   }
 }
@@ -195,7 +197,12 @@ struct lmpc_handle {
   // device staging for host-pointer calls
   DevBuf d_x0, d_rot, d_foot, d_cmd, d_contact, d_q, d_r, d_mu, d_fz, d_mass, d_inertia;
   DevBuf d_grf, d_status, d_iters, d_active, d_U;
-  DevBuf d_stats, d_counter, d_ws, d_wsA, d_wsT1, d_wsT2, d_order;
+  DevBuf d_stats, d_counter, d_ws, d_wsA, d_wsT1, d_wsT2, d_order, d_warm;
+  bool warm_enabled = false;
+  int warm_shift = 1;
+  // closed-loop rollout state (lmpc_rollout)
+  DevBuf d_rx, d_rfw, d_rph, d_rgait, d_rspeed, d_rtot, d_xlog, d_glog;
+  cudaEvent_t ev_r0 = nullptr, ev_r1 = nullptr;
   cudaEvent_t ev_cls = nullptr;
   int* h_cls = nullptr;  // pinned: n_max, |A|, |B|
   KStats last_stats;
@@ -284,11 +291,14 @@ extern "C" void lmpc_destroy(lmpc_handle* h) {
   if (h->stream) cudaStreamSynchronize(h->stream);
   DevBuf* bufs[] = {&h->d_x0, &h->d_rot, &h->d_foot, &h->d_cmd, &h->d_contact, &h->d_q, &h->d_r, &h->d_mu,
                     &h->d_fz, &h->d_mass, &h->d_inertia, &h->d_grf, &h->d_status, &h->d_iters, &h->d_active,
-                    &h->d_U, &h->d_stats, &h->d_counter, &h->d_ws, &h->d_wsA, &h->d_wsT1, &h->d_wsT2, &h->d_order};
+                    &h->d_U, &h->d_stats, &h->d_counter, &h->d_ws, &h->d_wsA, &h->d_wsT1, &h->d_wsT2, &h->d_order, &h->d_warm,
+                    &h->d_rx, &h->d_rfw, &h->d_rph, &h->d_rgait, &h->d_rspeed, &h->d_rtot, &h->d_xlog, &h->d_glog};
   for (DevBuf* b : bufs) b->release();
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
   if (h->ev_cls) cudaEventDestroy(h->ev_cls);
+  if (h->ev_r0) cudaEventDestroy(h->ev_r0);
+  if (h->ev_r1) cudaEventDestroy(h->ev_r1);
   if (h->h_cls) cudaFreeHost(h->h_cls);
   if (h->stream) cudaStreamDestroy(h->stream);
   delete h;
@@ -321,6 +331,8 @@ static lmpc_status launch_tile(lmpc_handle* h, const KBatch& kb, cudaStream_t s,
 // launch of the largest class, while the others run.
 static lmpc_status launch_solve(lmpc_handle* h, KBatch kb, cudaStream_t s) {
   const int H = h->kp.H;
+  kb.warm = h->warm_enabled ? (uint8_t*)h->d_warm.p : nullptr;
+  kb.warm_shift = h->warm_shift;
   KStats* dstats = (KStats*)h->d_stats.p;
   int* ctr = (int*)h->d_counter.p;  // [0..3] work counters, [4..7] class sizes
   int* order = (int*)h->d_order.p;  // class c at order + c * max_batch
@@ -432,6 +444,7 @@ static KBatch device_batch(const lmpc_batch_in* in, const lmpc_batch_out* out, i
   kb.grf = out->grf; kb.status = out->status; kb.iters = out->iters; kb.active = out->active_set; kb.U = out->U;
   kb.order = nullptr;
   kb.B = batch;
+  kb.warm = nullptr; kb.warm_shift = 0;
   return kb;
 }
 
@@ -496,6 +509,7 @@ extern "C" lmpc_status lmpc_solve(lmpc_handle* h, int32_t batch, const lmpc_batc
   kb.grf = (double*)h->d_grf.p; kb.status = out->status ? (int*)h->d_status.p : nullptr;
   kb.iters = out->iters ? (int*)h->d_iters.p : nullptr; kb.active = out->active_set ? (uint32_t*)h->d_active.p : nullptr;
   kb.U = out->U ? (double*)h->d_U.p : nullptr; kb.order = nullptr; kb.B = batch;
+  kb.warm = nullptr; kb.warm_shift = 0;
   st = launch_solve(h, kb, s);
   if (st != LMPC_OK) return st;
   CK(cudaMemcpyAsync(out->grf, kb.grf, B * 12 * 8, cudaMemcpyDeviceToHost, s));
@@ -506,10 +520,31 @@ extern "C" lmpc_status lmpc_solve(lmpc_handle* h, int32_t batch, const lmpc_batc
   return finish_solve(h, s);
 }
 
+extern "C" lmpc_status lmpc_set_warm_start(lmpc_handle* h, int32_t enable, int32_t horizon_shift) {
+  if (!h) { set_err("NULL handle"); return LMPC_ERR_INVALID_ARG; }
+  if (horizon_shift < 0 || horizon_shift > LMPC_MAX_HORIZON) { set_err("horizon_shift out of range"); return LMPC_ERR_INVALID_ARG; }
+  CK(cudaSetDevice(h->device));
+  if (enable && !h->d_warm.p) {
+    const size_t bytes = (size_t)h->max_batch * lmpc::warm_stride(h->kp.H);
+    CK(h->d_warm.ensure(bytes));
+    CK(cudaMemsetAsync(h->d_warm.p, 0, bytes, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+  }
+  h->warm_enabled = enable != 0;
+  h->warm_shift = horizon_shift;
+  return LMPC_OK;
+}
+
 extern "C" lmpc_status lmpc_reset_warm_start(lmpc_handle* h) {
   if (!h) { set_err("NULL handle"); return LMPC_ERR_INVALID_ARG; }
-  return LMPC_OK;  // every solve of this build is a cold start; nothing is cached on the device
+  if (!h->d_warm.p) return LMPC_OK;  // nothing is cached on the device
+  CK(cudaSetDevice(h->device));
+  CK(cudaMemsetAsync(h->d_warm.p, 0, (size_t)h->max_batch * lmpc::warm_stride(h->kp.H), h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  return LMPC_OK;
 }
+
+extern "C" int64_t lmpc_last_warm_hits(const lmpc_handle* h) { return h ? (int64_t)h->last_stats.warm_hits : 0; }
 
 extern "C" int64_t lmpc_launch_count(const lmpc_handle* h) { return h ? h->launches : 0; }
 extern "C" float lmpc_last_kernel_ms(const lmpc_handle* h) { return h ? h->last_ms : 0.f; }
@@ -521,5 +556,101 @@ extern "C" lmpc_status lmpc_last_stats(const lmpc_handle* h, double* mean_n_eff,
   if (mean_n_eff) *mean_n_eff = (double)h->last_stats.sum_n / np;
   if (mean_fact) *mean_fact = (double)h->last_stats.sum_fact / np;
   if (flops_executed) *flops_executed = h->last_stats.flops;
+  return LMPC_OK;
+}
+
+// ---------------------------------------------------------------- closed-loop rollout (config 5)
+
+extern "C" lmpc_status lmpc_rollout(lmpc_handle* h, int32_t batch, const lmpc_rollout_cfg* cfg,
+                                    const lmpc_rollout_state* st, lmpc_rollout_result* res) {
+  if (!h || !cfg || !st || !res) { set_err("NULL handle/cfg/state/result"); return LMPC_ERR_INVALID_ARG; }
+  if (batch < 1 || batch > h->max_batch) { set_err("batch must be in [1, max_batch]"); return LMPC_ERR_INVALID_ARG; }
+  if (cfg->steps < 1) { set_err("steps must be >= 1"); return LMPC_ERR_INVALID_ARG; }
+  if (!st->x || !st->foot_world || !st->phase || !st->gait || !st->gait_speed || !st->cmd) {
+    set_err("x, foot_world, phase, gait, gait_speed, cmd are required"); return LMPC_ERR_INVALID_ARG;
+  }
+  CK(cudaSetDevice(h->device));
+  cudaStream_t s = h->stream;
+  const int H = h->kp.H;
+  const size_t B = (size_t)batch, S = (size_t)cfg->steps;
+  const bool dev = st->on_device != 0;
+  if (!h->ev_r0) { CK(cudaEventCreate(&h->ev_r0)); CK(cudaEventCreate(&h->ev_r1)); }
+  if (cfg->warm_start) {
+    lmpc_status w = lmpc_set_warm_start(h, 1, 1);
+    if (w != LMPC_OK) return w;
+    if (cfg->warm_start == 1) { w = lmpc_reset_warm_start(h); if (w != LMPC_OK) return w; }  // 2: keep the faces of the previous call
+  } else {
+    h->warm_enabled = false;
+  }
+  // solver input/output arrays owned by the handle
+  CK(h->d_x0.ensure(B * 12 * 8)); CK(h->d_rot.ensure(B * 9 * 8)); CK(h->d_foot.ensure(B * 12 * 8));
+  CK(h->d_contact.ensure(B * 4 * H)); CK(h->d_grf.ensure(B * 12 * 8));
+  CK(h->d_rtot.ensure(sizeof(lmpc::RolloutTotals)));
+  CK(cudaMemsetAsync(h->d_rtot.p, 0, sizeof(lmpc::RolloutTotals), s));
+  lmpc::RolloutDev D;
+  memset(&D, 0, sizeof(D));
+  const double* d_cmd = st->cmd;
+  if (dev) {
+    D.x = st->x; D.foot_world = st->foot_world; D.phase = st->phase; D.gait = st->gait; D.gait_speed = st->gait_speed;
+    D.x_log = res->x_log; D.grf_log = res->grf_log;
+  } else {
+    CK(h->d_rx.ensure(B * 12 * 8)); CK(h->d_rfw.ensure(B * 12 * 8)); CK(h->d_rph.ensure(B * 4 * 8));
+    CK(h->d_rgait.ensure(B * 4)); CK(h->d_rspeed.ensure(B * 8)); CK(h->d_cmd.ensure(B * 9 * 8));
+    CK(cudaMemcpyAsync(h->d_rx.p, st->x, B * 12 * 8, cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(h->d_rfw.p, st->foot_world, B * 12 * 8, cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(h->d_rph.p, st->phase, B * 4 * 8, cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(h->d_rgait.p, st->gait, B * 4, cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(h->d_rspeed.p, st->gait_speed, B * 8, cudaMemcpyHostToDevice, s));
+    CK(cudaMemcpyAsync(h->d_cmd.p, st->cmd, B * 9 * 8, cudaMemcpyHostToDevice, s));
+    D.x = (double*)h->d_rx.p; D.foot_world = (double*)h->d_rfw.p; D.phase = (double*)h->d_rph.p;
+    D.gait = (const int*)h->d_rgait.p; D.gait_speed = (const double*)h->d_rspeed.p;
+    d_cmd = (const double*)h->d_cmd.p;
+    if (res->x_log) { CK(h->d_xlog.ensure(S * B * 12 * 8)); D.x_log = (double*)h->d_xlog.p; }
+    if (res->grf_log) { CK(h->d_glog.ensure(S * B * 12 * 8)); D.grf_log = (double*)h->d_glog.p; }
+  }
+  D.cmd = d_cmd;
+  D.x0 = (double*)h->d_x0.p; D.rot = (double*)h->d_rot.p; D.foot_abs = (double*)h->d_foot.p;
+  D.contact = (uint8_t*)h->d_contact.p; D.grf = (const double*)h->d_grf.p; D.B = batch;
+  lmpc::RolloutCfgDev C;
+  for (int i = 0; i < 12; ++i) C.foot_rel[i] = cfg->default_foot_pos_rel[i];
+  C.dlim_x = cfg->foot_delta_x_limit > 0 ? cfg->foot_delta_x_limit : 0.8;  // FOOT_DELTA_X_LIMIT, LeggedParams.h:29
+  C.dlim_y = cfg->foot_delta_y_limit > 0 ? cfg->foot_delta_y_limit : 0.8;  // FOOT_DELTA_Y_LIMIT, LeggedParams.h:30
+  C.ground_z = cfg->ground_z;
+  KBatch kb;
+  memset(&kb, 0, sizeof(kb));
+  kb.x0 = D.x0; kb.rot = D.rot; kb.foot = D.foot_abs; kb.cmd = d_cmd; kb.contact = D.contact;
+  kb.grf = (double*)h->d_grf.p; kb.B = batch;
+  const int tpb = 128, nblk = (batch + tpb - 1) / tpb;
+  CK(cudaEventRecord(h->ev_r0, s));
+  for (int step = 0; step < cfg->steps; ++step) {
+    lmpc::rollout_prepare_kernel<<<nblk, tpb, 0, s>>>(h->kp, D, C);
+    h->launches++;
+    lmpc_status r = launch_solve(h, kb, s);
+    if (r != LMPC_OK) return r;
+    lmpc::rollout_step_kernel<<<nblk, tpb, 0, s>>>(h->kp, D, nullptr, nullptr, (const KStats*)h->d_stats.p,
+                                                   (lmpc::RolloutTotals*)h->d_rtot.p, step);
+    h->launches++;
+  }
+  CK(cudaGetLastError());
+  CK(cudaEventRecord(h->ev_r1, s));
+  lmpc::RolloutTotals tot;
+  CK(cudaMemcpyAsync(&tot, h->d_rtot.p, sizeof(tot), cudaMemcpyDeviceToHost, s));
+  if (res->grf) CK(cudaMemcpyAsync(res->grf, h->d_grf.p, B * 12 * 8, dev ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, s));
+  if (!dev) {
+    CK(cudaMemcpyAsync(st->x, D.x, B * 12 * 8, cudaMemcpyDeviceToHost, s));
+    CK(cudaMemcpyAsync(st->foot_world, D.foot_world, B * 12 * 8, cudaMemcpyDeviceToHost, s));
+    CK(cudaMemcpyAsync(st->phase, D.phase, B * 4 * 8, cudaMemcpyDeviceToHost, s));
+    if (res->x_log) CK(cudaMemcpyAsync(res->x_log, D.x_log, S * B * 12 * 8, cudaMemcpyDeviceToHost, s));
+    if (res->grf_log) CK(cudaMemcpyAsync(res->grf_log, D.grf_log, S * B * 12 * 8, cudaMemcpyDeviceToHost, s));
+  }
+  CK(cudaStreamSynchronize(s));
+  CK(cudaEventElapsedTime(&res->device_ms, h->ev_r0, h->ev_r1));
+  res->solves = (int64_t)tot.solves; res->factorizations = (int64_t)tot.sum_fact; res->polish_rounds = (int64_t)tot.sum_polish;
+  res->not_converged = (int64_t)tot.not_ok; res->warm_hits = (int64_t)tot.warm_hits; res->flops_executed = tot.flops;
+  res->mean_n_eff = tot.solves ? (double)tot.sum_n / (double)tot.solves : 0.0;
+  if (tot.not_ok > 0) {
+    set_err(std::to_string((unsigned long long)tot.not_ok) + " solve(s) of the rollout did not converge (grf zeroed for that tick)");
+    return LMPC_ERR_NOT_CONVERGED;
+  }
   return LMPC_OK;
 }

@@ -3,6 +3,7 @@
 #include <string.h>
 
 #include "../../include/lmpc.h"
+#include "lmpc_gait.h"
 
 namespace {
 
@@ -33,42 +34,6 @@ void base(lmpc_params* p, int H, double dt, int disc, int scal, int off, const d
   for (int i = 0; i < 12; ++i) p->r[i] = 1e-4;  // r_weights_*, yaml :58-72
 }
 
-// Gait tables: (state, switch_time) per leg.  1 = STANCE, 0 = SWING (LeggedContactFSM.h:11-15).
-struct GaitLeg { int n; int state[3]; double sw[3]; };
-
-GaitLeg gait_table(int gait, int leg) {
-  GaitLeg t = {1, {1, 1, 1}, {1.0, 1.0, 1.0}};
-  const bool diagA = (leg == 0 || leg == 3);
-  switch (gait) {
-    case LMPC_GAIT_TROT:  // set_default_gait_pattern, LeggedContactFSM.cpp:93-114
-      t.n = 2; t.sw[0] = 0.5; t.sw[1] = 1.0;
-      t.state[0] = diagA ? 1 : 0; t.state[1] = diagA ? 0 : 1;
-      break;
-    case LMPC_GAIT_TROT_WITH_STAND:  // :116-157
-      if (diagA) { t.n = 2; t.state[0] = 1; t.state[1] = 0; t.sw[0] = 0.6; t.sw[1] = 1.0; }
-      else { t.n = 3; t.state[0] = 1; t.state[1] = 0; t.state[2] = 1; t.sw[0] = 0.1; t.sw[1] = 0.5; t.sw[2] = 1.0; }
-      break;
-    case LMPC_GAIT_CRAWL:  // :158-199
-      if (leg == 0) { t.n = 2; t.state[0] = 0; t.state[1] = 1; t.sw[0] = 0.25; t.sw[1] = 1.0; }
-      else if (leg == 1) { t.n = 3; t.state[0] = 1; t.state[1] = 0; t.state[2] = 1; t.sw[0] = 0.25; t.sw[1] = 0.5; t.sw[2] = 1.0; }
-      else if (leg == 2) { t.n = 3; t.state[0] = 1; t.state[1] = 0; t.state[2] = 1; t.sw[0] = 0.5; t.sw[1] = 0.75; t.sw[2] = 1.0; }
-      else { t.n = 2; t.state[0] = 1; t.state[1] = 0; t.sw[0] = 0.75; t.sw[1] = 1.0; }
-      break;
-    case LMPC_GAIT_STAND:  // :201-212
-      break;
-    case LMPC_GAIT_BOUND: {
-      const bool front = (leg == 0 || leg == 1);
-      t.n = 2; t.sw[0] = 0.5; t.sw[1] = 1.0;
-      t.state[0] = front ? 1 : 0; t.state[1] = front ? 0 : 1;
-      break;
-    }
-    default:  // LMPC_GAIT_PRONK
-      t.n = 2; t.sw[0] = 0.5; t.sw[1] = 1.0; t.state[0] = 1; t.state[1] = 0;
-      break;
-  }
-  return t;
-}
-
 }  // namespace
 
 extern "C" lmpc_status lmpc_params_preset(const char* name, lmpc_params* p) {
@@ -83,12 +48,7 @@ extern "C" lmpc_status lmpc_params_preset(const char* name, lmpc_params* p) {
 
 extern "C" int32_t lmpc_gait_predict_contact(int32_t gait, int32_t leg, double phase,
                                              double gait_speed, double delta_t) {
-  const GaitLeg t = gait_table(gait, leg);
-  double ph = phase + gait_speed * delta_t;  // LeggedContactFSM.cpp:281
-  while (ph > 1.0) ph -= 1.0;                // :283-285
-  for (int i = 0; i < t.n; ++i)              // :287-291
-    if (ph <= t.sw[i]) return t.state[i];
-  return 1;                                  // :293 "should not reach here" -> STANCE
+  return lmpc::gait_predict(gait, leg, phase, gait_speed, delta_t);
 }
 
 extern "C" lmpc_status lmpc_gait_contact_table(int32_t batch, int32_t horizon, double dt,

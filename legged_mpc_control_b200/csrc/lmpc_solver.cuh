@@ -492,10 +492,13 @@ __device__ void solve_one(const KParams& P, const KBatch& Bt, KStats* stats, con
   bool solved = false;
   // three accuracy stages: polish after mu <= 1e-7; if the face guess does not verify, continue
   // to 1e-10 and retry; finally accept the interior-point answer at 1e-13.
-  for (int stage = 0; stage < 3 && !solved; ++stage) {
-    const double mu_tol = stage == 0 ? 1e-7 : (stage == 1 ? 1e-10 : 1e-13);
+  // warm start: see solve_one_warp
+  uint8_t* wrec = Bt.warm ? Bt.warm + (size_t)warm_stride(H) * p64 : nullptr;
+  const bool warm = wrec && wrec[4 * H] != 0;
+  for (int stage = warm ? -1 : 0; stage < 3 && !solved; ++stage) {
+    const double mu_tol = stage <= 0 ? 1e-7 : (stage == 1 ? 1e-10 : 1e-13);
     bool ipm_converged = false, ipm_broken = false;
-    while (n_ipm < max_iter) {
+    while (stage >= 0 && n_ipm < max_iter) {
       // residuals at the current iterate
       symv<NT>(Hs, n, u, tmp);
       __syncthreads();
@@ -633,7 +636,10 @@ __device__ void solve_one(const KParams& P, const KBatch& Bt, KStats* stats, con
     // ---------------- stage 4b: exact active-set polish on the identified pyramid faces
     // face per block: sx, sy in {-1, 0, +1} (fx = sx mu fz / fy = sy mu fz pinned), top (fz = fmax),
     // apex (f = 0).  u_b = T_b v_b + p_b with the shear T_b = I + mu (sx e_x + sy e_y) e_z'.
-    {
+    if (stage < 0) {
+      for (int b = tid; b < nb; b += NT) warm_face_load(wrec, H, Bt.warm_shift, blk[2 * b], blk[2 * b + 1], face + 4 * b);
+      __syncthreads();
+    } else {
       double smax = 0, zmax = 0;
       for (int b = tid; b < nb; b += NT) {
         double s[5];
@@ -814,7 +820,16 @@ __device__ void solve_one(const KParams& P, const KBatch& Bt, KStats* stats, con
       __syncthreads();
       for (int w = tid; w < W; w += NT) Bt.active[(size_t)W * p64 + w] = aw[w];
     }
+    if (wrec) {
+      __syncthreads();  // every thread has read the record-valid byte
+      for (int idx = tid; idx < 4 * H; idx += NT) {
+        const int b = bmap[idx];
+        wrec[idx] = (status == 0 && b >= 0) ? face_encode(face + 4 * b) : (unsigned char)0;
+      }
+      if (tid == 0) wrec[4 * H] = status == 0 ? 1 : 0;
+    }
     if (tid == 0) {
+      if (status == 0 && n_ipm == 0) atomicAdd(&stats->warm_hits, 1ull);
       const int nf = n_ipm + n_polish;
       if (Bt.status) Bt.status[p64] = status;
       if (Bt.iters) Bt.iters[p64] = (nf & 0xffff) | (n_polish << 16);

@@ -330,13 +330,16 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
   int n_ipm = 0, n_polish = 0, status = -1;
   const int max_iter = P.max_iter;
   bool solved = false;
+  // warm start: see solve_one_warp
+  uint8_t* wrec = Bt.warm ? Bt.warm + (size_t)warm_stride(H) * p64 : nullptr;
+  const bool warm = wrec && wrec[4 * H] != 0;
 #pragma unroll 1
-  for (int stage = 0; stage < 3 && !solved; ++stage) {
-    const double mu_tol = stage == 0 ? P.tol0 : (stage == 1 ? 1e-10 : 1e-13);
-    const double rdt = stage == 0 ? rd_tol0 : rd_tol;
+  for (int stage = warm ? -1 : 0; stage < 3 && !solved; ++stage) {
+    const double mu_tol = stage <= 0 ? P.tol0 : (stage == 1 ? 1e-10 : 1e-13);
+    const double rdt = stage <= 0 ? rd_tol0 : rd_tol;
     bool ipm_converged = false, ipm_broken = false;
 #pragma unroll 1
-    while (n_ipm < max_iter) {
+    while (stage >= 0 && n_ipm < max_iter) {
       double rdinf = 0, sz = 0;
       for (int b = lane; b < nb; b += 32) {
         double s[5], ct[3];
@@ -501,7 +504,10 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
     }
 
     // ---------------- stage 4b: exact active-set polish on the identified pyramid faces
-    {
+    if (stage < 0) {
+      for (int b = lane; b < nb; b += 32) warm_face_load(wrec, H, Bt.warm_shift, blk[2 * b], blk[2 * b + 1], face + 4 * b);
+      __syncwarp();
+    } else {
       double smax = 0, zmax = 0;
       for (int b = lane; b < nb; b += 32) {
         double s[5];
@@ -684,11 +690,19 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
       __syncwarp();
       for (int w = lane; w < W; w += 32) Bt.active[(size_t)W * p64 + w] = aw[w];
     }
+    if (wrec) {
+      for (int idx = lane; idx < 4 * H; idx += 32) {
+        const int b = bmap[idx];
+        wrec[idx] = (status == 0 && b >= 0) ? face_encode(face + 4 * b) : (unsigned char)0;
+      }
+      if (lane == 0) wrec[4 * H] = status == 0 ? 1 : 0;
+    }
     const int nf = n_ipm + n_polish;
     if (lane == 0) {
       if (Bt.status) Bt.status[p64] = status;
       if (Bt.iters) Bt.iters[p64] = (nf & 0xffff) | (n_polish << 16);
     }
+    if (status == 0 && n_ipm == 0) ws.warm_hits++;
     ws.problems++; ws.sum_n += n; ws.sum_fact += nf; ws.sum_polish += n_polish;
     if (status >= 2) ws.not_ok++;
     if (status == 1) ws.ipm_only++;

@@ -41,7 +41,30 @@ struct KBatch {
   double* U;             // may be nullptr
   const int* order;      // optional problem permutation (size-class sorted), nullptr -> identity
   int B;
+  // Warm start (OSQP warm-start analogue, ConvexQPSolver.cpp:185): per problem 4H face bytes
+  // (one per step x leg, see face_encode) + 4 header bytes (byte 4H: record valid).  nullptr -> cold.
+  uint8_t* warm;
+  int warm_shift;        // horizon steps elapsed since the stored solve (1 when control dt == MPC dt)
 };
+
+__host__ __device__ inline int warm_stride(int H) { return 4 * H + 4; }
+
+// One byte per stance block: bit 7 valid, bits 0-1 sx+1, bits 2-3 sy+1, bit 4 top, bit 5 apex.
+__host__ __device__ inline unsigned char face_encode(const signed char* f) {
+  return (unsigned char)(0x80 | (f[0] + 1) | ((f[1] + 1) << 2) | ((f[2] & 1) << 4) | ((f[3] & 1) << 5));
+}
+// Face guess of block (step k, leg) from the record stored `shift` steps ago; interior if unknown.
+__host__ __device__ inline void warm_face_load(const uint8_t* rec, int H, int shift, int k, int leg, signed char* f) {
+  int kk = k + shift;
+  if (kk > H - 1) kk = H - 1;
+  const unsigned char c = rec[4 * kk + leg];
+  if (c & 0x80) {
+    f[0] = (signed char)((c & 3) - 1); f[1] = (signed char)(((c >> 2) & 3) - 1);
+    f[2] = (signed char)((c >> 4) & 1); f[3] = (signed char)((c >> 5) & 1);
+  } else {
+    f[0] = 0; f[1] = 0; f[2] = 0; f[3] = 0;
+  }
+}
 
 // Per-launch statistics accumulated with atomics (bench evidence).
 struct KStats {
@@ -51,6 +74,7 @@ struct KStats {
   unsigned long long sum_polish;   // polish rounds only
   unsigned long long not_ok;       // problems with status >= 2
   unsigned long long ipm_only;     // problems with status == 1
+  unsigned long long warm_hits;    // problems solved from the stored faces alone (no interior-point iteration)
   double flops;                    // executed factorization+solve flops (n^3/3 + 4n^2 per factorization etc.)
   int n_max;                       // max reduced dimension seen by the classify pass
 };

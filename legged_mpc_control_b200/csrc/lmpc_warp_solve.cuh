@@ -44,7 +44,7 @@ __host__ __device__ inline WarpPlan make_warp_plan(int H) {
 }
 
 struct WarpStats {
-  unsigned long long problems = 0, sum_n = 0, sum_fact = 0, sum_polish = 0, not_ok = 0, ipm_only = 0;
+  unsigned long long problems = 0, sum_n = 0, sum_fact = 0, sum_polish = 0, not_ok = 0, ipm_only = 0, warm_hits = 0;
   double flops = 0;
 };
 
@@ -253,6 +253,11 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
         const int lo = 32 * w, hi = min(32 * w + 32, 24 * H);
         Bt.active[(size_t)W * p64 + w] = (hi - lo == 32) ? 0xffffffffu : ((1u << (hi - lo)) - 1u);
       }
+    if (Bt.warm) {
+      uint8_t* wrec = Bt.warm + (size_t)warm_stride(H) * p64;
+      for (int i = lane; i < 4 * H; i += 32) wrec[i] = 0;
+      if (lane == 0) wrec[4 * H] = 1;
+    }
     ws.problems++;
     __syncwarp();
     return;
@@ -374,13 +379,18 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
   int n_ipm = 0, n_polish = 0, status = -1;
   const int max_iter = P.max_iter;
   bool solved = false;
+  // Warm start: stage -1 skips the interior point and hands the faces stored by the previous solve
+  // of this problem (shifted along the horizon) straight to the exact polish; if they do not verify
+  // within its repair rounds the cold path runs as usual.
+  uint8_t* wrec = Bt.warm ? Bt.warm + (size_t)warm_stride(H) * p64 : nullptr;
+  const bool warm = wrec && wrec[4 * H] != 0;
 #pragma unroll 1
-  for (int stage = 0; stage < 3 && !solved; ++stage) {
-    const double mu_tol = stage == 0 ? P.tol0 : (stage == 1 ? 1e-10 : 1e-13);
-    const double rdt = stage == 0 ? rd_tol0 : rd_tol;
+  for (int stage = warm ? -1 : 0; stage < 3 && !solved; ++stage) {
+    const double mu_tol = stage <= 0 ? P.tol0 : (stage == 1 ? 1e-10 : 1e-13);
+    const double rdt = stage <= 0 ? rd_tol0 : rd_tol;
     bool ipm_converged = false, ipm_broken = false;
 #pragma unroll 1
-    while (n_ipm < max_iter) {
+    while (stage >= 0 && n_ipm < max_iter) {
       double s[5], is[5], w[5], rdv[3] = {0.0, 0.0, 0.0}, ctz[3] = {0.0, 0.0, 0.0};
       double wb[6] = {0, 0, 0, 0, 0, 0};  // C_b' W C_b: (0,0) (2,0) (1,1) (2,1) (2,2); (1,0) = 0
       double rdinf = 0, sz = 0;
@@ -529,7 +539,10 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
     }
 
     // ---------------- stage 4b: exact active-set polish on the identified pyramid faces
-    {
+    if (stage < 0) {
+      if (act) warm_face_load(wrec, H, Bt.warm_shift, blk[2 * lane], blk[2 * lane + 1], face + 4 * lane);
+      __syncwarp();
+    } else {
       double smax = 0, zmax = 0;
       double s[5];
       blk_slack(uf, mu, fzm, s);
@@ -710,12 +723,20 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
       __syncwarp();
       for (int w = lane; w < W; w += 32) Bt.active[(size_t)W * p64 + w] = aw[w];
     }
+    if (wrec) {  // faces of the verified solution for the next solve of this problem
+      for (int idx = lane; idx < 4 * H; idx += 32) {
+        const int b = bmap[idx];
+        wrec[idx] = (status == 0 && b >= 0) ? face_encode(face + 4 * b) : (unsigned char)0;
+      }
+      if (lane == 0) wrec[4 * H] = status == 0 ? 1 : 0;
+    }
     if (lane == 0) {
       const int nf = n_ipm + n_polish;
       if (Bt.status) Bt.status[p64] = status;
       if (Bt.iters) Bt.iters[p64] = (nf & 0xffff) | (n_polish << 16);
     }
     const int nf = n_ipm + n_polish;
+    if (status == 0 && n_ipm == 0) ws.warm_hits++;
     ws.problems++; ws.sum_n += n; ws.sum_fact += nf; ws.sum_polish += n_polish;
     if (status >= 2) ws.not_ok++;
     if (status == 1) ws.ipm_only++;

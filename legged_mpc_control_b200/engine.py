@@ -72,8 +72,63 @@ class ConvexMpcEngine:
             raise LmpcError(st, _lib.last_error())
         return st
 
+    def set_warm_start(self, enable: bool, horizon_shift: int = 1):
+        """OSQP warm-start analogue (ConvexQPSolver.cpp:185): reuse the previous solve's pyramid faces
+        of the same batch index, shifted `horizon_shift` steps (lmpc_set_warm_start)."""
+        st = self._L.lmpc_set_warm_start(self._h, 1 if enable else 0, int(horizon_shift))
+        if st != abi.OK:
+            raise LmpcError(st, _lib.last_error())
+
     def reset_warm_start(self):
         self._L.lmpc_reset_warm_start(self._h)
+
+    @property
+    def last_warm_hits(self) -> int:
+        return int(self._L.lmpc_last_warm_hits(self._h))
+
+    # -- closed-loop batched rollout (BASELINE config 5), state resident on the device between steps
+    def rollout(self, state: dict, steps: int, foot_rel, warm_start: int = 1, ground_z: float = 0.0,
+                log: bool = False, on_device: bool = False) -> dict:
+        """state: x [B,12], foot_world [B,12], phase [B,4], gait [B] int32, gait_speed [B], cmd [B,9]
+        — numpy arrays (updated in place) or, with on_device=True, a dict of device pointers plus
+        'batch'.  Returns the counters of lmpc_rollout_result (+ logs / last GRFs for host arrays)."""
+        cfg = abi.LmpcRolloutCfg()
+        cfg.steps, cfg.warm_start, cfg.ground_z = int(steps), int(warm_start), float(ground_z)
+        fr = np.ascontiguousarray(foot_rel, np.float64).reshape(-1)
+        for i in range(12):
+            cfg.default_foot_pos_rel[i] = fr[i]
+        st = abi.LmpcRolloutState()
+        res = abi.LmpcRolloutResult()
+        out = {}
+        if on_device:
+            B = int(state["batch"])
+            for k in ("x", "foot_world", "phase", "gait", "gait_speed", "cmd"):
+                setattr(st, k, state[k])
+            st.on_device = 1
+            res.grf, res.x_log, res.grf_log = state.get("grf"), state.get("x_log"), state.get("grf_log")
+        else:
+            spec = (("x", np.float64, 12), ("foot_world", np.float64, 12), ("phase", np.float64, 4), ("gait", np.int32, 1),
+                    ("gait_speed", np.float64, 1), ("cmd", np.float64, 9))
+            B = np.asarray(state["x"]).size // 12
+            for k, dt, per in spec:
+                a = state[k]
+                if not (isinstance(a, np.ndarray) and a.dtype == dt and a.flags.c_contiguous and a.size == B * per):
+                    raise ValueError(f"rollout state '{k}' must be a C-contiguous {np.dtype(dt).name} array of {B}x{per}")
+                setattr(st, k, a.ctypes.data)
+            st.on_device = 0
+            out["grf"] = np.zeros((B, 12))
+            res.grf = out["grf"].ctypes.data
+            if log:
+                out["x_log"] = np.zeros((steps, B, 12))
+                out["grf_log"] = np.zeros((steps, B, 12))
+                res.x_log, res.grf_log = out["x_log"].ctypes.data, out["grf_log"].ctypes.data
+        rc = self._L.lmpc_rollout(self._h, B, C.byref(cfg), C.byref(st), C.byref(res))
+        if rc not in (abi.OK, abi.ERR_NOT_CONVERGED):
+            raise LmpcError(rc, _lib.last_error())
+        out.update(rc=rc, solves=res.solves, factorizations=res.factorizations, polish_rounds=res.polish_rounds,
+                   not_converged=res.not_converged, warm_hits=res.warm_hits, flops_executed=res.flops_executed,
+                   mean_n_eff=res.mean_n_eff, device_ms=res.device_ms)
+        return out
 
     @property
     def launch_count(self) -> int:

@@ -117,6 +117,36 @@ def make_batch(n: int, horizon: int, dt: float, seed: int, robot: str = "a1", ga
     return out
 
 
+def make_rollout_state(n: int, seed: int, robot: str = "a1", gaits=(abi.GAIT_TROT,), start: int = 0, gait_speed=None):
+    """Initial closed-loop state of robots [start, start+n) for lmpc_rollout (config 5): level trunk
+    at standing height with small random attitude/velocity, feet on the ground under the hips,
+    random gait phase and joystick command.  Returns the dict lmpc_rollout_state expects."""
+    idx = np.arange(start, start + n, dtype=np.uint64)
+    f = lambda fld, lo, hi: uniform(seed, idx, fld, lo, hi)  # noqa: E731
+    fh = np.asarray(presets.footholds(robot), np.float64)  # [4][3]
+    z0 = -fh[0, 2]
+    yaw = f(3, -np.pi, np.pi)
+    x = np.stack([f(1, -0.05, 0.05), f(2, -0.05, 0.05), yaw, f(4, -1, 1), f(5, -1, 1), z0 + f(6, -0.02, 0.02),
+                  normal(seed, idx, 7, 0.1), normal(seed, idx, 8, 0.1), normal(seed, idx, 9, 0.1),
+                  f(10, -0.3, 0.3), f(11, -0.3, 0.3), normal(seed, idx, 12, 0.05)], axis=1)
+    cy, sy = np.cos(yaw), np.sin(yaw)
+    fw = np.zeros((n, 4, 3))
+    for leg in range(4):
+        fw[:, leg, 0] = x[:, 3] + cy * fh[leg, 0] - sy * fh[leg, 1]
+        fw[:, leg, 1] = x[:, 4] + sy * fh[leg, 0] + cy * fh[leg, 1]
+    cmd = np.stack([np.zeros(n), np.zeros(n), np.full(n, z0), f(41, -1.0, 1.0), f(42, -0.3, 0.3), np.zeros(n),
+                    np.zeros(n), np.zeros(n), f(43, -0.8, 0.8)], axis=1)
+    gaits = list(gaits)
+    gsel = np.minimum((u01(seed, idx, 50) * len(gaits)).astype(np.int64), len(gaits) - 1)
+    if gait_speed is None:
+        gait_speed = presets.A1_GAIT_SPEED if robot == "a1" else presets.GO1_GAIT_SPEED
+    return {"x": np.ascontiguousarray(x), "foot_world": np.ascontiguousarray(fw.reshape(n, 12)),
+            "phase": np.ascontiguousarray(np.repeat(u01(seed, idx, 51)[:, None], 4, axis=1)),
+            "gait": np.ascontiguousarray(np.asarray(gaits, np.int32)[gsel]),
+            "gait_speed": np.full(n, float(gait_speed)), "cmd": np.ascontiguousarray(cmd),
+            "foot_rel": np.ascontiguousarray(fh.reshape(12))}
+
+
 def standing_problem(horizon: int, robot: str = "a1", z: float = 0.28, contact_all: bool = True):
     """Deterministic C1 state: euler=0, pos=(0,0,z), zero velocities, feet at the yaml footholds,
     z_d=z (fixture idea from the reference's test_wbc.cpp:126-129: f_z = m g / 4 per leg)."""

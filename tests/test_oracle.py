@@ -274,3 +274,44 @@ def test_oracle_nan_rule(oracle):
     b["x0"][0, 0] = np.nan
     out = oracle.solve_batch(p, b, eliminate_swing=True)
     assert out["status"][0] != 0 and np.all(out["grf"][0] == 0) and out["status"][1] == 0
+
+
+def test_rollout_twin_closed_loop_is_stable(oracle):
+    """numpy rollout twin (oracle/rollout_np.py): 8 trotting A1s for 60 control steps keep their
+    commanded height and attitude; swing legs carry no force; phases advance by speed*dt."""
+    from oracle import rollout_np
+    p = presets.preset("northstar_a1")
+    st = synth.make_rollout_state(8, seed=5)
+    fr = st.pop("foot_rel")
+    ph0 = st["phase"].copy()
+    x_log, g_log = rollout_np.rollout(p, st, 60, fr)
+    assert np.abs(x_log[-1][:, 5] - st["cmd"][:, 2]).max() < 0.03
+    assert np.abs(x_log[:, :, 0:2]).max() < 0.2
+    adv = (st["phase"] - ph0 - 60 * st["gait_speed"][:, None] * p.dt) % 1.0
+    assert np.minimum(adv, 1.0 - adv).max() < 1e-9
+    # trot: the diagonal pair in swing has exactly zero force in every step
+    f = g_log.reshape(60, 8, 4, 3)
+    assert ((np.abs(f[:, :, [0, 3]]).sum(axis=(2, 3)) == 0) | (np.abs(f[:, :, [1, 2]]).sum(axis=(2, 3)) == 0)).all()
+
+
+def test_rollout_twin_plant_matches_step_matrices(oracle):
+    """prepare() hands the solver exactly the state it integrates: foot_pos_abs = foot_world - pos,
+    rot = Rz Ry Rx(euler) and the Raibert target of BaseInterface.cpp:358-399 for swing legs."""
+    from oracle import rollout_np
+    p = presets.preset("reference_a1")
+    st = synth.make_rollout_state(4, seed=9)
+    fr = st.pop("foot_rel")
+    b = rollout_np.prepare(p, st, fr)
+    assert np.allclose(b["foot_pos_abs"].reshape(4, 4, 3), st["foot_world"].reshape(4, 4, 3) - st["x"][:, None, 3:6])
+    R = b["rot"].reshape(4, 3, 3).transpose(0, 2, 1)
+    assert np.allclose(R @ R.transpose(0, 2, 1), np.eye(3)[None], atol=1e-14)
+    i = 0
+    c0 = b["contact"].reshape(4, p.horizon, 4)[i, 0]
+    leg = int(np.nonzero(c0 == 0)[0][0])
+    x = st["x"][i]
+    cy, sy = np.cos(x[2]), np.sin(x[2])
+    vd = np.array([cy * st["cmd"][i, 3] - sy * st["cmd"][i, 4], sy * st["cmd"][i, 3] + cy * st["cmd"][i, 4]])
+    k = np.sqrt(abs(x[5]) / 9.8)
+    delta = k * (x[9:11] - vd) + (1.0 / st["gait_speed"][i] / 2.0) / 2.0 * vd
+    hip = np.array([cy * fr[3 * leg] - sy * fr[3 * leg + 1], sy * fr[3 * leg] + cy * fr[3 * leg + 1]])
+    assert np.allclose(st["foot_world"][i, 3 * leg:3 * leg + 2], hip + delta + x[3:5])
