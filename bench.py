@@ -34,11 +34,31 @@ SEED = 3
 L2_FLUSH_BYTES = 256 << 20
 
 
+# name -> (preset, seed, robot, gaits, per-problem params, label); BASELINE.json configs
+WORKLOADS = {
+    "headline": (PRESET, SEED, "a1", (abi.GAIT_TROT,), False, "a1_trot"),                                  # metric config
+    "c3": ("northstar_go1_h20", 2, "go1", (abi.GAIT_TROT, abi.GAIT_BOUND, abi.GAIT_PRONK), False, "go1_mixed_gaits"),  # config 3
+    "ref_h30": ("reference_a1", 6, "a1", (abi.GAIT_TROT, abi.GAIT_TROT_WITH_STAND, abi.GAIT_CRAWL, abi.GAIT_STAND), False,
+                "a1_reference_preset_all_gaits"),                                                          # the reference's own H=30
+    "sweep": (PRESET, 4, "a1", (abi.GAIT_TROT, abi.GAIT_BOUND, abi.GAIT_PRONK), True, "a1_param_sweep"),   # config 4
+}
+_WL = "headline"
+
+
+def make_workload(B, start):
+    preset_name, seed, robot, gaits, per, _ = WORKLOADS[_WL]
+    p = presets.preset(preset_name)
+    kw = {"gait_speed": (2.0, 4.5)} if per else {}
+    return p, synth.make_batch(B, p.horizon, p.dt, seed=seed, robot=robot, gaits=gaits, start=start,
+                               per_problem_params=per, base_params=p if per else None, **kw)
+
+
 def workload_config(n_gpus, batch):
-    p = presets.preset(PRESET)
+    preset_name, seed, _, _, _, label = WORKLOADS[_WL]
+    p = presets.preset(preset_name)
     return {
-        "workload": f"a1_trot_h{p.horizon}_dt{p.dt}_batch{batch}_seed{SEED}",
-        "preset": PRESET, "horizon": p.horizon, "dt": p.dt, "batch_per_gpu": batch,
+        "workload": f"{label}_h{p.horizon}_dt{p.dt}_batch{batch}_seed{seed}",
+        "preset": preset_name, "horizon": p.horizon, "dt": p.dt, "batch_per_gpu": batch,
         "global_batch": batch * n_gpus, "parallelism": f"batch-shard x{n_gpus} (no collective)",
         "l2": "flushed between timed steps (256 MiB write)",
     }
@@ -52,12 +72,12 @@ def cpu_sample(p, seconds_target=12.0, threads=None):
     ob.build()
     threads = threads or (os.cpu_count() or 1)
     pilot_n = 32 * threads
-    b = synth.make_batch(pilot_n, p.horizon, p.dt, seed=SEED)
+    _, b = make_workload(pilot_n, 0)
     t0 = time.perf_counter()
     ob.solve_batch(p, b, eliminate_swing=True, nthreads=threads, want_kkt=False)
     pilot = time.perf_counter() - t0
     n = int(min(BATCH, max(pilot_n, pilot_n * seconds_target / max(pilot, 1e-3))))
-    b = synth.make_batch(n, p.horizon, p.dt, seed=SEED)
+    _, b = make_workload(n, 0)
     t0 = time.perf_counter()
     out = ob.solve_batch(p, b, eliminate_swing=True, nthreads=threads, want_kkt=False)
     dt = time.perf_counter() - t0
@@ -72,7 +92,7 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    p = presets.preset(PRESET)
+    p = presets.preset(WORKLOADS[_WL][0])
     vals = []
     sample = ""
     cores = os.cpu_count() or 1
@@ -141,11 +161,11 @@ def run_b200(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
-    p = presets.preset(PRESET)
-    H, B = p.horizon, args.batch
     # weak scaling: rank r solves problems [r*B, (r+1)*B) of the stream
-    batch = synth.make_batch(B, H, p.dt, seed=SEED, start=rank * B)
-    names = ("x0", "rot", "foot_pos_abs", "cmd", "contact")
+    B = args.batch
+    p, batch = make_workload(B, rank * B)
+    H = p.horizon
+    names = tuple(k for k in ("x0", "rot", "foot_pos_abs", "cmd", "contact", "q", "r", "mu") if k in batch)
     tin = {k: torch.from_numpy(batch[k]).to(dev) for k in names}
     W = abi.active_words(H)
     tout = {"grf": torch.zeros(B, 12, dtype=torch.float64, device=dev),
@@ -201,8 +221,11 @@ def run_b200(args):
     barrier()
     t0 = time.perf_counter()
     e2e_steps = max(3, min(args.steps, 10))
+    e2e_lat = []
     for _ in range(e2e_steps):
-        out = eng.compute_grfs(hb, want_U=False)
+        t1 = time.perf_counter()
+        out = eng.compute_grfs(hb, want_U=False)  # blocking: returns after the D2H copies
+        e2e_lat.append(time.perf_counter() - t1)
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
     te = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
@@ -277,11 +300,12 @@ def run_b200(args):
             "p50_batch_latency_ms": float(np.median([a.elapsed_time(b) for a, b in ev])),
             "clocks": sampler.summary(),
             "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                    "steps": e2e_steps, "api": "ConvexMpcEngine.compute_grfs -> lmpc_solve (host pointers)"},
+                    "steps": e2e_steps, "p50_batch_latency_ms": 1e3 * float(np.median(e2e_lat)), "api": "ConvexMpcEngine.compute_grfs -> lmpc_solve (host pointers)"},
             "gpu_launches": int(launches),
             "roofline": {
                 "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-                "traffic": None, "kernel": "lmpc::solve_warp_kernel", "kernel_ms": kms,
+                "traffic": None, "kernel": "lmpc::solve_warp_kernel" if stats["mean_n_eff"] <= 63 else "lmpc::solve_tile_kernel / solve_kernel (by size class)",
+                "kernel_ms": kms,
                 "precision": "fp64", "peak_source": "measured on this GPU by lmpc_microbench_fp64 (MEASURED_PEAKS.json has no FP64 entry)",
                 "fp64_peaks_tflops": peaks,
                 "flops_per_launch_executed": stats["flops_executed"], "mean_n_eff": stats["mean_n_eff"],
@@ -372,13 +396,17 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=BATCH)
     ap.add_argument("--no-warm", action="store_true", help="skip the warm-started re-solve measurement")
-    ap.add_argument("--workload", default="headline", choices=["headline", "rollout"],
-                    help="rollout: BASELINE config 5 (16384 robots x --rollout-steps control steps, closed loop on device)")
+    ap.add_argument("--workload", default="headline", choices=["headline", "c3", "ref_h30", "sweep", "rollout"],
+                    help="headline: the metric's config (default); c3 / sweep: BASELINE configs 3 / 4; ref_h30: the reference's own "
+                         "H=30 preset; rollout: config 5 (16384 robots x --rollout-steps control steps, closed loop on device)")
     ap.add_argument("--rollout-steps", type=int, default=1000)
     ap.add_argument("--robots", type=int, default=16384)
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = 3  # timing rule: W >= 3
+    global _WL
+    if args.workload != "rollout":
+        _WL = args.workload
     if args.impl == "reference":
         run_reference(args)
     elif args.workload == "rollout":
