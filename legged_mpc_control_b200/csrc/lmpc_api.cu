@@ -170,6 +170,7 @@ extern "C" int32_t lmpc_abi_version(void) { return LMPC_ABI_VERSION; }
   } while (0)
 
 static constexpr int kThreads = 64;
+static constexpr int kThreadsSpill = 256;
 
 struct DevBuf {
   void* p = nullptr;
@@ -387,10 +388,13 @@ static lmpc_status launch_solve(lmpc_handle* h, KBatch kb, cudaStream_t s) {
         pl = lmpc::make_plan(H, ncap, false);
         if (pl.total_bytes > h->smem_optin) { set_err("shared-memory plan does not fit even with spilled matrices"); return LMPC_ERR_INVALID_ARG; }
       }
-      auto kern = lmpc::solve_kernel<kThreads>;
+      // matrices in L2: latency bound, so more rows in flight per column (256 threads) pays
+      int nthr = in_smem ? kThreads : kThreadsSpill;
+      if (const char* e = getenv("LMPC_CLS3_THREADS")) nthr = atoi(e) == 64 ? 64 : (atoi(e) == 128 ? 128 : (atoi(e) == 512 ? 512 : 256));
+      auto kern = nthr == 64 ? lmpc::solve_kernel<64> : (nthr == 128 ? lmpc::solve_kernel<128> : (nthr == 512 ? lmpc::solve_kernel<512> : lmpc::solve_kernel<256>));
       CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total_bytes));
       int occ = 0;
-      CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, kThreads, pl.total_bytes));
+      CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, nthr, pl.total_bytes));
       if (occ < 1) { set_err("solve kernel does not fit on an SM"); return LMPC_ERR_CUDA; }
       int grid = h->num_sms * occ;
       if (grid > countB) grid = countB;
@@ -402,7 +406,7 @@ static lmpc_status launch_solve(lmpc_handle* h, KBatch kb, cudaStream_t s) {
       }
       KBatch kbB = kb;
       kbB.order = order + 3 * (size_t)stride;
-      kern<<<grid, kThreads, pl.total_bytes, s>>>(h->kp, kbB, dstats, ncap, in_smem, gws, ctr + 7, ctr + 3);
+      kern<<<grid, nthr, pl.total_bytes, s>>>(h->kp, kbB, dstats, ncap, in_smem, gws, ctr + 7, ctr + 3);
       h->launches++;
       CK(cudaGetLastError());
     }

@@ -625,9 +625,7 @@ __device__ void solve_one(const KParams& P, const KBatch& Bt, KStats* stats, con
       }
       __syncthreads();
     }
-    if (ipm_broken) { status = 3; break; }
-
-    if (stage == 2) {
+    if (stage == 2 && !ipm_broken) {  // (a broken interior point still gets one polish: see solve_one_warp)
       status = ipm_converged ? 1 : 2;
       solved = ipm_converged;
       break;
@@ -767,7 +765,13 @@ __device__ void solve_one(const KParams& P, const KBatch& Bt, KStats* stats, con
         face[4 * b] = (signed char)sx; face[4 * b + 1] = (signed char)sy; face[4 * b + 2] = (signed char)top; face[4 * b + 3] = (signed char)apex;
       }
       if (changed) atomicOr(&si[INT_CHANGED], 1);
+      {  // NaN compares false everywhere above: a non-finite solve must never pass as verified
+        double fsum = 0.0;
+        for (int i = tid; i < n; i += NT) fsum += dua[i] + tmp[i] + gs[i];
+        if (!isfinite(fsum)) atomicOr(&si[INT_CHANGED], 2);
+      }
       __syncthreads();
+      if (si[INT_CHANGED] & 2) break;
       if (si[INT_CHANGED] == 0) { polished = true; break; }
       __syncthreads();
     }
@@ -776,6 +780,9 @@ __device__ void solve_one(const KParams& P, const KBatch& Bt, KStats* stats, con
       __syncthreads();
       status = 0;
       solved = true;
+    } else if (ipm_broken) {
+      status = 3;
+      break;
     }
     // else: keep the interior iterate (u, z untouched by the polish) and tighten mu
   }

@@ -496,8 +496,7 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
       blk_store<NT>(Hg, b, hd);
     }
     __syncwarp();
-    if (ipm_broken) { status = 3; break; }
-    if (stage == 2) {
+    if (stage == 2 && !ipm_broken) {  // (a broken interior point still gets one polish: see solve_one_warp)
       status = ipm_converged ? 1 : 2;
       solved = ipm_converged;
       break;
@@ -535,13 +534,19 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
       // p (pinned particular solution) in rd ; hu = H p
       for (int i = lane; i < N; i += 32) rd[i] = 0.0;
       __syncwarp();
+      bool pinned_top = false;
       for (int b = lane; b < nb; b += 32) {
         const int sx = face[4 * b], sy = face[4 * b + 1], top = face[4 * b + 2], apex = face[4 * b + 3];
+        pinned_top = pinned_top || (top && !apex);
         const double pz = (top && !apex) ? fzm : 0.0;
         rd[3 * b] = sx * mu * pz; rd[3 * b + 1] = sy * mu * pz; rd[3 * b + 2] = pz;
       }
       __syncwarp();
-      gm_symv<NT>(Hg, rd, hu);
+      if (__any_sync(0xffffffffu, pinned_top)) {
+        gm_symv<NT>(Hg, rd, hu);
+      } else {  // p = 0: H p = 0 without reading H
+        for (int i = lane; i < N; i += 32) hu[i] = 0.0;
+      }
       __syncwarp();
       // Mt = T' H T with pinned rows/cols replaced by identity, written into the factor storage
       {
@@ -638,7 +643,11 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
         face[4 * b] = (signed char)sx; face[4 * b + 1] = (signed char)sy; face[4 * b + 2] = (signed char)top; face[4 * b + 3] = (signed char)apex;
       }
       const bool any_changed = __any_sync(0xffffffffu, changed);
+      double fsum = 0.0;  // NaN compares false everywhere above: a non-finite solve must never pass as verified
+      for (int i = lane; i < N; i += 32) fsum += dua[i] + hu[i] + gs[i];
+      const bool finite = !__any_sync(0xffffffffu, !isfinite(fsum));
       __syncwarp();
+      if (!finite) break;
       if (!any_changed) { polished = true; break; }
     }
     if (polished) {
@@ -646,6 +655,9 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
       __syncwarp();
       status = 0;
       solved = true;
+    } else if (ipm_broken) {
+      status = 3;
+      break;
     } else {
       // back to the interior point at a tighter mu: H u of the interior iterate is needed again
       gm_symv<NT>(Hg, u, hu);

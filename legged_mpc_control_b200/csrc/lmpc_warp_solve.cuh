@@ -531,8 +531,9 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
       __stcg(Hg + moff[5], hd[4]); __stcg(Hg + moff[7], hd[4]);
     }
     __syncwarp();
-    if (ipm_broken) { status = 3; break; }
-    if (stage == 2) {
+    // a broken interior point (non-finite iterate, non-positive pivot) still gets one exact polish
+    // from the last good iterate's faces: the polish verifies KKT itself, so this can only help
+    if (stage == 2 && !ipm_broken) {
       status = ipm_converged ? 1 : 2;
       solved = ipm_converged;
       break;
@@ -567,14 +568,20 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
       // p (pinned particular solution) in rd ; hu = Hs p
       rd[lane] = 0.0; rd[lane + 32] = 0.0;
       __syncwarp();
+      bool pinned_top = false;
       if (lane < nb) {
         const int b = lane;
         const int sx = face[4 * b], sy = face[4 * b + 1], top = face[4 * b + 2], apex = face[4 * b + 3];
-        const double pz = (top && !apex) ? fzm : 0.0;
+        pinned_top = top && !apex;
+        const double pz = pinned_top ? fzm : 0.0;
         rd[3 * b] = sx * mu * pz; rd[3 * b + 1] = sy * mu * pz; rd[3 * b + 2] = pz;
       }
       __syncwarp();
-      wm_symv(Hg, rd, hu);
+      if (__any_sync(0xffffffffu, pinned_top)) {
+        wm_symv(Hg, rd, hu);
+      } else {  // p = 0 (no force pinned at fz_max, the usual case): H p = 0 without reading H
+        hu[lane] = 0.0; hu[lane + 32] = 0.0;
+      }
       __syncwarp();
       // Mt = T' Hs T with pinned rows/cols replaced by identity, written into the panel storage
       {
@@ -675,7 +682,10 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
         face[4 * b] = (signed char)sx; face[4 * b + 1] = (signed char)sy; face[4 * b + 2] = (signed char)top; face[4 * b + 3] = (signed char)apex;
       }
       const bool any_changed = __any_sync(0xffffffffu, changed);
+      // NaN compares false everywhere above: a non-finite solve must never pass as verified
+      const bool finite = !__any_sync(0xffffffffu, !isfinite(dua[lane] + dua[lane + 32] + hu[lane] + hu[lane + 32] + gs[lane] + gs[lane + 32]));
       __syncwarp();
+      if (!finite) break;
       if (!any_changed) { polished = true; break; }
     }
     if (polished) {
@@ -683,6 +693,9 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
       __syncwarp();
       status = 0;
       solved = true;
+    } else if (ipm_broken) {
+      status = 3;
+      break;
     }
   }
   if (status < 0) status = 2;

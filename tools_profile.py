@@ -13,8 +13,11 @@ reps = int(sys.argv[3]) if len(sys.argv) > 3 else 3
 p = presets.preset(name)
 from legged_mpc_control_b200 import abi
 go1 = "go1" in name
-b = synth.make_batch(B, p.horizon, p.dt, seed=2 if go1 else 3, robot="go1" if go1 else "a1",
-                     gaits=(abi.GAIT_TROT, abi.GAIT_BOUND, abi.GAIT_PRONK) if go1 else (abi.GAIT_TROT,))
+gaits = (abi.GAIT_TROT, abi.GAIT_BOUND, abi.GAIT_PRONK) if go1 else (abi.GAIT_TROT,)
+if len(sys.argv) > 4:
+    gaits = tuple({"trot": abi.GAIT_TROT, "stand": abi.GAIT_STAND, "crawl": abi.GAIT_CRAWL, "tws": abi.GAIT_TROT_WITH_STAND,
+                   "bound": abi.GAIT_BOUND, "pronk": abi.GAIT_PRONK}[g] for g in sys.argv[4].split(","))
+b = synth.make_batch(B, p.horizon, p.dt, seed=2 if go1 else 3, robot="go1" if go1 else "a1", gaits=gaits)
 dev = torch.device("cuda:0")
 tin = {k: torch.from_numpy(b[k]).to(dev) for k in ("x0", "rot", "foot_pos_abs", "cmd", "contact")}
 grf = torch.zeros(B, 12, dtype=torch.float64, device=dev)
