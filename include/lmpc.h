@@ -28,6 +28,7 @@
 #ifndef LMPC_H_
 #define LMPC_H_
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -182,6 +183,11 @@ lmpc_status lmpc_reset_warm_start(lmpc_handle* h);
 int64_t lmpc_last_warm_hits(const lmpc_handle* h);
 
 void lmpc_destroy(lmpc_handle* h);
+
+/* Page-locked host buffers for host-pointer lmpc_solve calls (full-rate H2D/D2H copies); plain
+ * malloc'ed memory works too, just slower.  NULL on failure. */
+void* lmpc_alloc_pinned(size_t bytes);
+void lmpc_free_pinned(void* p);
 
 /* Thread-local, never NULL. */
 const char* lmpc_last_error_string(void);

@@ -14,7 +14,7 @@ EXPORTS = (
     "lmpc_reset_warm_start", "lmpc_destroy", "lmpc_last_error_string", "lmpc_abi_version",
     "lmpc_launch_count", "lmpc_last_kernel_ms", "lmpc_last_stats", "lmpc_gait_predict_contact",
     "lmpc_gait_contact_table", "lmpc_microbench_fp64", "lmpc_set_warm_start", "lmpc_last_warm_hits",
-    "lmpc_rollout",
+    "lmpc_rollout", "lmpc_alloc_pinned", "lmpc_free_pinned",
 )
 
 
@@ -48,6 +48,10 @@ def lib():
     L.lmpc_last_warm_hits.restype = C.c_int64
     L.lmpc_rollout.argtypes = [C.c_void_p, C.c_int32, C.POINTER(abi.LmpcRolloutCfg), C.POINTER(abi.LmpcRolloutState),
                                C.POINTER(abi.LmpcRolloutResult)]
+    L.lmpc_alloc_pinned.argtypes = [C.c_size_t]
+    L.lmpc_alloc_pinned.restype = C.c_void_p
+    L.lmpc_free_pinned.argtypes = [C.c_void_p]
+    L.lmpc_free_pinned.restype = None
     L.lmpc_destroy.argtypes = [C.c_void_p]
     L.lmpc_destroy.restype = None
     L.lmpc_last_stats.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double)]

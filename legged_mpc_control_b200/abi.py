@@ -166,16 +166,22 @@ def host_batch_in(batch: dict, horizon: int):
     return s, keep, nb
 
 
-def host_batch_out(nb: int, horizon: int, want_U: bool = True):
-    """Allocate numpy outputs and an LmpcBatchOut over them."""
-    out = {
-        "grf": np.zeros((nb, 12), np.float64),
-        "status": np.full((nb,), -1, np.int32),
-        "iters": np.zeros((nb,), np.int32),
-        "active_set": np.zeros((nb, active_words(horizon)), np.uint32),
-    }
+def out_spec(nb: int, horizon: int, want_U: bool = True):
+    """(name, shape, dtype) of every lmpc_batch_out array."""
+    spec = [("grf", (nb, 12), np.float64), ("status", (nb,), np.int32), ("iters", (nb,), np.int32),
+            ("active_set", (nb, active_words(horizon)), np.uint32)]
     if want_U:
-        out["U"] = np.zeros((nb, 12 * horizon), np.float64)
+        spec.append(("U", (nb, 12 * horizon), np.float64))
+    return spec
+
+
+def host_batch_out(nb: int, horizon: int, want_U: bool = True, arrays: dict = None):
+    """Allocate numpy outputs (or use `arrays`, e.g. pinned views) and an LmpcBatchOut over them."""
+    if arrays is None:
+        out = {name: np.zeros(shape, dt) for name, shape, dt in out_spec(nb, horizon, want_U)}
+        out["status"][:] = -1
+    else:
+        out = dict(arrays)
     s = LmpcBatchOut()
     s.grf = out["grf"].ctypes.data
     s.status = out["status"].ctypes.data

@@ -241,6 +241,8 @@ static void fill_kparams(const lmpc_params& p, KParams* k) {
   if (const char* e = getenv("LMPC_TOL0")) k->tol0 = atof(e);
   if (const char* e = getenv("LMPC_RDTOL0")) k->rdtol0 = atof(e);
   if (const char* e = getenv("LMPC_FZ0")) k->fz0 = atof(e);
+  k->try_interior = 0;
+  if (const char* e = getenv("LMPC_TRY_INTERIOR")) k->try_interior = atoi(e);
   for (int i = 0; i < 9; ++i) k->inertia[i] = p.inertia[i];
   for (int i = 0; i < 12; ++i) { k->q[i] = p.q[i]; k->r[i] = p.r[i]; }
 }
@@ -549,6 +551,15 @@ extern "C" lmpc_status lmpc_reset_warm_start(lmpc_handle* h) {
 }
 
 extern "C" int64_t lmpc_last_warm_hits(const lmpc_handle* h) { return h ? (int64_t)h->last_stats.warm_hits : 0; }
+
+// Page-locked host memory for callers without a CUDA runtime of their own (the ctypes mirror):
+// host-pointer lmpc_solve calls copy at full PCIe rate only from/to pinned buffers.
+extern "C" void* lmpc_alloc_pinned(size_t bytes) {
+  void* p = nullptr;
+  if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) { set_err("cudaMallocHost failed"); return nullptr; }
+  return p;
+}
+extern "C" void lmpc_free_pinned(void* p) { if (p) cudaFreeHost(p); }
 
 extern "C" int64_t lmpc_launch_count(const lmpc_handle* h) { return h ? h->launches : 0; }
 extern "C" float lmpc_last_kernel_ms(const lmpc_handle* h) { return h ? h->last_ms : 0.f; }

@@ -494,7 +494,7 @@ __device__ void solve_one(const KParams& P, const KBatch& Bt, KStats* stats, con
   // to 1e-10 and retry; finally accept the interior-point answer at 1e-13.
   // warm start: see solve_one_warp
   uint8_t* wrec = Bt.warm ? Bt.warm + (size_t)warm_stride(H) * p64 : nullptr;
-  const bool warm = wrec && wrec[4 * H] != 0;
+  const bool warm = wrec && (wrec[4 * H] != 0 || P.try_interior);
   for (int stage = warm ? -1 : 0; stage < 3 && !solved; ++stage) {
     const double mu_tol = stage <= 0 ? 1e-7 : (stage == 1 ? 1e-10 : 1e-13);
     bool ipm_converged = false, ipm_broken = false;

@@ -332,7 +332,7 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
   bool solved = false;
   // warm start: see solve_one_warp
   uint8_t* wrec = Bt.warm ? Bt.warm + (size_t)warm_stride(H) * p64 : nullptr;
-  const bool warm = wrec && wrec[4 * H] != 0;
+  const bool warm = wrec && (wrec[4 * H] != 0 || P.try_interior);
 #pragma unroll 1
   for (int stage = warm ? -1 : 0; stage < 3 && !solved; ++stage) {
     const double mu_tol = stage <= 0 ? P.tol0 : (stage == 1 ? 1e-10 : 1e-13);

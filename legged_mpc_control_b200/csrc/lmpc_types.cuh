@@ -16,6 +16,7 @@ struct KParams {
   double tol0;    // complementarity target of the first interior-point stage (then: exact polish)
   double rdtol0;  // relative dual-residual target of the first stage
   double fz0;     // initial fz as a fraction of fz_max (<= 0: m g / #stance legs of the step)
+  int try_interior; // experiment: cold problems first try the polish from all-interior faces
   double inertia[9];
   double q[12];
   double r[12];

@@ -383,7 +383,7 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
   // of this problem (shifted along the horizon) straight to the exact polish; if they do not verify
   // within its repair rounds the cold path runs as usual.
   uint8_t* wrec = Bt.warm ? Bt.warm + (size_t)warm_stride(H) * p64 : nullptr;
-  const bool warm = wrec && wrec[4 * H] != 0;
+  const bool warm = wrec && (wrec[4 * H] != 0 || P.try_interior);
 #pragma unroll 1
   for (int stage = warm ? -1 : 0; stage < 3 && !solved; ++stage) {
     const double mu_tol = stage <= 0 ? P.tol0 : (stage == 1 ? 1e-10 : 1e-13);

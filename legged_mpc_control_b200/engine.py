@@ -27,21 +27,48 @@ class ConvexMpcEngine:
         self.max_batch = int(max_batch)
         self.device = int(device)
         self._h = C.c_void_p()
+        self._pin_ptrs, self._pin_arrays, self._pin_key = [], None, None
         st = self._L.lmpc_create(C.byref(self.params), self.max_batch, self.device, C.byref(self._h))
         if st != abi.OK:
             raise LmpcError(st, _lib.last_error())
 
     # -- reference-shaped entry point: host arrays in, first-step GRFs (+ diagnostics) out
-    def compute_grfs(self, batch: dict, want_U: bool = True, strict: bool = False) -> dict:
+    def _pinned_out(self, nb: int, want_U: bool) -> dict:
+        """Engine-owned page-locked output arrays (lmpc_alloc_pinned), reused across calls."""
+        key = (nb, bool(want_U))
+        if self._pin_key != key:
+            self._free_pinned()
+            arrays = {}
+            for name, shape, dt in abi.out_spec(nb, self.params.horizon, want_U):
+                nbytes = int(np.prod(shape)) * np.dtype(dt).itemsize
+                ptr = self._L.lmpc_alloc_pinned(nbytes)
+                if not ptr:
+                    raise LmpcError(abi.ERR_ALLOC, _lib.last_error())
+                self._pin_ptrs.append(ptr)
+                arrays[name] = np.frombuffer((C.c_char * nbytes).from_address(ptr), dtype=dt).reshape(shape)
+            self._pin_arrays, self._pin_key = arrays, key
+        return self._pin_arrays
+
+    def _free_pinned(self):
+        self._pin_arrays, self._pin_key = None, None
+        for ptr in self._pin_ptrs:
+            self._L.lmpc_free_pinned(ptr)
+        self._pin_ptrs = []
+
+    def compute_grfs(self, batch: dict, want_U: bool = True, strict: bool = False, copy: bool = True) -> dict:
         """batch: dict of numpy arrays in the lmpc_batch_in layout.  Returns dict with grf [B,12],
-        status, iters (low 16 bits factorizations, high 16 polish rounds), active_set, U."""
+        status, iters (low 16 bits factorizations, high 16 polish rounds), active_set, U.
+        copy=False returns views of the engine's page-locked output buffers (valid until the next
+        call on this engine) — the zero-overhead form a control loop uses."""
         H = self.params.horizon
         sin, keep, nb = abi.host_batch_in(batch, H)
-        sout, out = abi.host_batch_out(nb, H, want_U)
+        sout, out = abi.host_batch_out(nb, H, want_U, arrays=self._pinned_out(nb, want_U))
         st = self._L.lmpc_solve(self._h, nb, C.byref(sin), C.byref(sout))
         del keep
         if st not in (abi.OK, abi.ERR_NOT_CONVERGED) or (strict and st != abi.OK):
             raise LmpcError(st, _lib.last_error())
+        if copy:
+            out = {k: v.copy() for k, v in out.items()}
         out["rc"] = st
         out["factorizations"] = out["iters"] & 0xFFFF
         out["polish_rounds"] = out["iters"] >> 16
@@ -144,6 +171,7 @@ class ConvexMpcEngine:
         return {"mean_n_eff": a.value, "mean_factorizations": b.value, "flops_executed": c.value}
 
     def close(self):
+        self._free_pinned()
         if self._h:
             self._L.lmpc_destroy(self._h)
             self._h = C.c_void_p()
