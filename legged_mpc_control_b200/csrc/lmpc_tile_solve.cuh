@@ -305,31 +305,9 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
     u[3 * b + 2] = fz_init;
   }
   __syncwarp();
-  {
-    gm_symv<NT>(Hg, u, hu);
-    __syncwarp();
-    double gi = 0, ssum = 0;
-    for (int i = lane; i < N; i += 32) gi = fmax(gi, fabs(hu[i] + gs[i]));
-    for (int b = lane; b < nb; b += 32) {
-      double s[5];
-      blk_slack(u + 3 * b, mu, fzm, s);
-      ssum += s[0] + s[1] + s[2] + s[3] + s[4];
-    }
-    const double ginf = wmax(gi);
-    ssum = wsum(ssum);
-    const double zc = (ginf > 1e-6 ? ginf : 1e-6) * (ssum * inv_m);
-    for (int b = lane; b < nb; b += 32) {
-      double s[5];
-      blk_slack(u + 3 * b, mu, fzm, s);
-#pragma unroll
-      for (int r = 0; r < 5; ++r) z[5 * b + r] = zc * frcp(s[r]);
-    }
-  }
-  __syncwarp();
-
   int n_ipm = 0, n_polish = 0, status = -1;
   const int max_iter = P.max_iter;
-  bool solved = false;
+  bool solved = false, ipm_inited = false;
   // warm start: see solve_one_warp
   uint8_t* wrec = Bt.warm ? Bt.warm + (size_t)warm_stride(H) * p64 : nullptr;
   const bool warm = wrec && (wrec[4 * H] != 0 || P.try_interior);
@@ -338,6 +316,30 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
     const double mu_tol = stage <= 0 ? P.tol0 : (stage == 1 ? 1e-10 : 1e-13);
     const double rdt = stage <= 0 ? rd_tol0 : rd_tol;
     bool ipm_converged = false, ipm_broken = false;
+    if (stage >= 0 && !ipm_inited) {  // interior-point start (skipped entirely by a verified warm start)
+      ipm_inited = true;
+      {
+        gm_symv<NT>(Hg, u, hu);
+        __syncwarp();
+        double gi = 0, ssum = 0;
+        for (int i = lane; i < N; i += 32) gi = fmax(gi, fabs(hu[i] + gs[i]));
+        for (int b = lane; b < nb; b += 32) {
+          double s[5];
+          blk_slack(u + 3 * b, mu, fzm, s);
+          ssum += s[0] + s[1] + s[2] + s[3] + s[4];
+        }
+        const double ginf = wmax(gi);
+        ssum = wsum(ssum);
+        const double zc = (ginf > 1e-6 ? ginf : 1e-6) * (ssum * inv_m);
+        for (int b = lane; b < nb; b += 32) {
+          double s[5];
+          blk_slack(u + 3 * b, mu, fzm, s);
+#pragma unroll
+          for (int r = 0; r < 5; ++r) z[5 * b + r] = zc * frcp(s[r]);
+        }
+      }
+      __syncwarp();
+    }
 #pragma unroll 1
     while (stage >= 0 && n_ipm < max_iter) {
       double rdinf = 0, sz = 0;

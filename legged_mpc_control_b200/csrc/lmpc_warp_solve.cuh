@@ -353,8 +353,16 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
   __syncwarp();
   if (act) u[3 * lane + 2] = uf[2];
   __syncwarp();
-  {
-    wm_symv(Hg, u, hu);
+  int n_ipm = 0, n_polish = 0, status = -1;
+  const int max_iter = P.max_iter;
+  bool solved = false;
+  // Warm start: stage -1 skips the interior point and hands the faces stored by the previous solve
+  // of this problem (shifted along the horizon) straight to the exact polish; if they do not verify
+  // within its repair rounds the cold path runs as usual.
+  uint8_t* wrec = Bt.warm ? Bt.warm + (size_t)warm_stride(H) * p64 : nullptr;
+  const bool warm = wrec && (wrec[4 * H] != 0 || P.try_interior);
+  {  // interior-point start
+    if (!warm) wm_symv(Hg, u, hu);  // a warm start defers this product until its faces fail to verify (hu = 0 here)
     __syncwarp();
     double ssum = 0, gi = 0;
     double s[5];
@@ -375,20 +383,19 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
 #pragma unroll
       for (int r = 0; r < 5; ++r) zr[r] = zc * frcp(s[r]);
   }
-
-  int n_ipm = 0, n_polish = 0, status = -1;
-  const int max_iter = P.max_iter;
-  bool solved = false;
-  // Warm start: stage -1 skips the interior point and hands the faces stored by the previous solve
-  // of this problem (shifted along the horizon) straight to the exact polish; if they do not verify
-  // within its repair rounds the cold path runs as usual.
-  uint8_t* wrec = Bt.warm ? Bt.warm + (size_t)warm_stride(H) * p64 : nullptr;
-  const bool warm = wrec && (wrec[4 * H] != 0 || P.try_interior);
 #pragma unroll 1
   for (int stage = warm ? -1 : 0; stage < 3 && !solved; ++stage) {
     const double mu_tol = stage <= 0 ? P.tol0 : (stage == 1 ? 1e-10 : 1e-13);
     const double rdt = stage <= 0 ? rd_tol0 : rd_tol;
     bool ipm_converged = false, ipm_broken = false;
+    if (stage == 0 && warm) {  // the stored faces did not verify: cold path after all, H u0 is needed now
+      wm_symv(Hg, u, hu);
+      __syncwarp();
+      if (act) {
+#pragma unroll
+        for (int a = 0; a < 3; ++a) huf[a] = hu[3 * lane + a];
+      }
+    }
 #pragma unroll 1
     while (stage >= 0 && n_ipm < max_iter) {
       double s[5], is[5], w[5], rdv[3] = {0.0, 0.0, 0.0}, ctz[3] = {0.0, 0.0, 0.0};
