@@ -23,6 +23,14 @@ namespace lmpc {
 //   1: 64 <= n <= 120     one warp per QP, 15 x 15 tiles      (solve_tile_kernel<15>)
 //   2: 121 <= n <= 192    one warp per QP, 24 x 24 tiles      (solve_tile_kernel<24>)
 //   3: n > 192            one CTA per QP, packed matrices     (solve_kernel)
+// Register cap of the one-warp kernel, measured on B200 (headline workload, solves/s):
+//   __launch_bounds__(32, 9): ptxas settles on 168 registers, 600 B of spills, 9 warps/SM   3.75 M
+//   __maxnreg__(224):         290 B of spills, 9 warps/SM                                   3.90 M
+//   __maxnreg__(255):         230 B of spills, 8 warps/SM                                   4.19 M
+// The kernel is latency-bound inside each warp, so fewer spills beat the ninth warp.
+#ifndef LMPC_WARP_MAXNREG
+#define LMPC_WARP_MAXNREG 255
+#endif
 constexpr int kNumClasses = 4;
 constexpr int kTileA = 15, kTileB = 24;
 __host__ __device__ inline int size_class(int n) {
@@ -98,7 +106,7 @@ __global__ void __launch_bounds__(32) solve_tile_kernel(const __grid_constant__ 
 // Persistent one-warp-per-QP solve (class A).  One warp per CTA: no block barrier exists in this
 // kernel.  Problems are handed out by an atomic counter; the scaled Hessian of the problem in
 // flight lives in this CTA's 32 KB slot of the L2-resident workspace `gws`.
-__global__ void __launch_bounds__(32, 9) solve_warp_kernel(const __grid_constant__ KParams P,
+__global__ void __maxnreg__(LMPC_WARP_MAXNREG) solve_warp_kernel(const __grid_constant__ KParams P,
                                                         const __grid_constant__ KBatch Bt,
                                                         KStats* stats, double* gws,
                                                         const int* __restrict__ count,
