@@ -133,3 +133,25 @@ def test_rollout_device_pointers_and_errors():
     with pytest.raises(LmpcError):
         eng.rollout(host, 0, fr)
     eng.close()
+
+
+def test_warm_equals_cold_at_headline_batch():
+    """Full 65 536-problem headline batch: a warm-started solve of a moved state returns the same
+    minimiser as a cold solve of it (size-independent property; both KKT-verified on device)."""
+    p = presets.preset("northstar_a1")
+    B = 65536
+    b0 = synth.make_batch(B, p.horizon, p.dt, seed=3)
+    b1 = dict(b0)
+    b1["x0"] = b0["x0"] + 1e-3 * np.random.default_rng(1).standard_normal(b0["x0"].shape)
+    eng = _engine(p, B)
+    cold = eng.compute_grfs(b1, want_U=False)
+    eng.set_warm_start(True, horizon_shift=0)
+    eng.compute_grfs(b0, want_U=False)
+    warm = eng.compute_grfs(b1, want_U=False)
+    assert eng.last_warm_hits > 0.99 * B
+    assert (warm["status"] <= abi.PROB_OK_IPM_ONLY).all() and (cold["status"] <= abi.PROB_OK_IPM_ONLY).all()
+    assert _rel_err(warm["grf"], cold["grf"]).max() <= REL_TOL
+    exact = (warm["status"] == 0) & (cold["status"] == 0)
+    assert np.array_equal(warm["active_set"][exact], cold["active_set"][exact])
+    assert warm["factorizations"].mean() < 0.15 * cold["factorizations"].mean()
+    eng.close()
