@@ -79,17 +79,24 @@ __device__ inline void flush_warp_stats(const WarpStats& ws, KStats* stats) {
   }
 }
 
-// Persistent one-warp-per-QP solve for 64 <= n <= 8 NT: fragment-ordered factor in shared memory
-// (61 KB at NT = 15: three warps per SM; 154 KB at NT = 24: one), Hessian slot in the L2 workspace.
-template <int NT>
-__global__ void __launch_bounds__(32) solve_tile_kernel(const __grid_constant__ KParams P,
-                                                        const __grid_constant__ KBatch Bt, KStats* stats,
-                                                        double* gws, const int* __restrict__ count,
-                                                        int* work_counter) {
+// Persistent solve for 64 <= n <= 8 NT, one QP per CTA of NW warps: fragment-ordered factor in shared
+// memory (61 KB at NT = 15, 154 KB at NT = 24), Hessian slot in the L2 workspace.  Warp 0 runs the
+// whole solve; warps 1 .. NW-1 only share the tile columns of every Cholesky factorization
+// (tile_helper_loop), which is where n >= 120 spends its time.
+template <int NT, int NW>
+__global__ void __maxnreg__(255) solve_tile_kernel(const __grid_constant__ KParams P,
+                                                             const __grid_constant__ KBatch Bt, KStats* stats,
+                                                             double* gws, const int* __restrict__ count,
+                                                             int* work_counter) {
   extern __shared__ __align__(16) unsigned char smem[];
   const TilePlan pl = make_tile_plan<NT>(P.H);
   constexpr size_t kSlot = (size_t)TileGeom<NT>::HS + 6 * TileGeom<NT>::NBMAX + 2;
   double* Hg = gws + (size_t)blockIdx.x * kSlot;
+  if (NW > 1 && threadIdx.x >= 32) {
+    double* sd = reinterpret_cast<double*>(smem);
+    tile_helper_loop<NT, NW>(Hg, sd + pl.oLS, sd + pl.oXB);
+    return;
+  }
   const int lane = threadIdx.x;
   const int total = *count;
   WarpStats ws;
@@ -98,9 +105,13 @@ __global__ void __launch_bounds__(32) solve_tile_kernel(const __grid_constant__ 
     if (lane == 0) w = atomicAdd(work_counter, 1);
     w = __shfl_sync(0xffffffffu, w, 0);
     if (w >= total) break;
-    solve_one_tile<NT>(P, Bt, ws, pl, smem, Hg, Bt.order[w]);
+    solve_one_tile<NT, NW>(P, Bt, ws, pl, smem, Hg, Bt.order[w]);
   }
   flush_warp_stats(ws, stats);
+  if (NW > 1) {
+    if (lane == 0) *tile_job() = 0;
+    __syncthreads();
+  }
 }
 
 // Persistent one-warp-per-QP solve (class A).  One warp per CTA: no block barrier exists in this
@@ -179,6 +190,7 @@ extern "C" int32_t lmpc_abi_version(void) { return LMPC_ABI_VERSION; }
 
 static constexpr int kThreads = 64;
 static constexpr int kThreadsSpill = 256;
+static constexpr int kTileWarpsA = 1, kTileWarpsB = 4;  // measured: NT=15 gains nothing from helpers (581k vs 587k/445k solves/s at 2/4 warps), NT=24 +31% at 4
 
 struct DevBuf {
   void* p = nullptr;
@@ -315,14 +327,14 @@ extern "C" void lmpc_destroy(lmpc_handle* h) {
   delete h;
 }
 
-template <int NT>
-static lmpc_status launch_tile(lmpc_handle* h, const KBatch& kb, cudaStream_t s, DevBuf* wsbuf, int* order, int* count,
-                               int* work) {
+template <int NT, int NW>
+static lmpc_status launch_tile_nw(lmpc_handle* h, const KBatch& kb, cudaStream_t s, DevBuf* wsbuf, int* order, int* count,
+                                  int* work) {
   const lmpc::TilePlan tp = lmpc::make_tile_plan<NT>(h->kp.H);
-  auto kern = lmpc::solve_tile_kernel<NT>;
+  auto kern = lmpc::solve_tile_kernel<NT, NW>;
   CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tp.total_bytes));
   int occ = 0;
-  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 32, tp.total_bytes));
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 32 * NW, tp.total_bytes));
   if (occ < 1) { set_err("tile solve kernel does not fit on an SM"); return LMPC_ERR_CUDA; }
   int grid = h->num_sms * occ;
   if (grid > kb.B) grid = kb.B;
@@ -330,10 +342,20 @@ static lmpc_status launch_tile(lmpc_handle* h, const KBatch& kb, cudaStream_t s,
   CK(wsbuf->ensure((size_t)grid * slot * sizeof(double)));
   KBatch k = kb;
   k.order = order;
-  kern<<<grid, 32, tp.total_bytes, s>>>(h->kp, k, (KStats*)h->d_stats.p, (double*)wsbuf->p, count, work);
+  kern<<<grid, 32 * NW, tp.total_bytes, s>>>(h->kp, k, (KStats*)h->d_stats.p, (double*)wsbuf->p, count, work);
   h->launches++;
   CK(cudaGetLastError());
   return LMPC_OK;
+}
+// Warps per QP of the tile classes (LMPC_TILE_NW overrides for experiments: 1, 2 or 4).
+template <int NT>
+static lmpc_status launch_tile(lmpc_handle* h, const KBatch& kb, cudaStream_t s, DevBuf* wsbuf, int* order, int* count,
+                               int* work) {
+  int nw = NT == lmpc::kTileA ? kTileWarpsA : kTileWarpsB;
+  if (const char* e = getenv("LMPC_TILE_NW")) nw = atoi(e);
+  if (nw == 1) return launch_tile_nw<NT, 1>(h, kb, s, wsbuf, order, count, work);
+  if (nw == 2) return launch_tile_nw<NT, 2>(h, kb, s, wsbuf, order, count, work);
+  return launch_tile_nw<NT, 4>(h, kb, s, wsbuf, order, count, work);
 }
 
 // Launch classify + the per-size-class solves on `s` for the device-resident batch `kb`.  The

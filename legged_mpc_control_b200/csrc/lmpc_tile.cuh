@@ -88,6 +88,110 @@ __device__ __noinline__ bool gm_factor(const double* Mg, double* Ls, double* xb)
   return ok;
 }
 
+// ---- the same factorization spread over the NW warps of a CTA (one QP per CTA) ----
+// Warp W owns the tiles i = W, W + NW, ... of every tile column; all warps meet at two CTA barriers
+// per column (inverse of the diagonal tile published; column final).  W is a template parameter so
+// that accumulator indices stay static; a helper warp whose share of a late column is empty only
+// passes the barriers.  Everything else of the solve stays on warp 0.
+template <int NT, int CNT, bool FROM_G, int NW, int W>
+__device__ __forceinline__ bool gm_column_mw(const double2* Mf, double2* Lf, double* xb) {
+  using G = TileGeom<NT>;
+  constexpr int J = NT - CNT;
+  constexpr int CW = CNT > W ? (CNT - W + NW - 1) / NW : 0;  // tiles of this column owned by warp W
+  double2* colL = Lf + 32 * G::lcol(J);
+  const double2* colM = Mf + 32 * (J * NT + J);
+  double2 acc[CW > 0 ? CW : 1];
+#pragma unroll
+  for (int m = 0; m < CW; ++m) {
+    const int i = W + NW * m;
+    const double2 v = FROM_G ? __ldcg(colM + 32 * NT * i) : colL[32 * i];
+    acc[m] = make_double2(-v.x, -v.y);
+  }
+  if (J > 0 && CW > 0) {
+    const double2* p = Lf + 32 * J;
+#pragma unroll 1
+    for (int K = 0; K < J; ++K) {  // acc[m] += L_{J+i,K} L_{J,K}'
+      const double2 bj = p[0];
+#pragma unroll
+      for (int m = 0; m < CW; ++m) dmma_xyt(acc[m], p[32 * (W + NW * m)], bj);
+      p += 32 * (NT - K - 1);
+    }
+  }
+  bool bad = false;
+  if (W == 0) {
+    const double2 li0 = wm_diag8u(-acc[0].x, -acc[0].y, xb);
+    colL[0] = li0;
+    bad = !(li0.x == li0.x) || !(li0.y == li0.y);
+  }
+  __syncthreads();  // inv(L_JJ) visible to every warp
+  if (CW > (W == 0 ? 1 : 0)) {
+    const double2 li = colL[0];
+    const double2 nli = make_double2(-li.x, -li.y);
+#pragma unroll
+    for (int m = (W == 0 ? 1 : 0); m < CW; ++m) {
+      double2 x = make_double2(0.0, 0.0);
+      dmma_xyt(x, acc[m], nli);
+      colL[32 * (W + NW * m)] = x;
+    }
+  }
+  __syncthreads();  // column J final
+  return bad;
+}
+template <int NT, int CNT, bool FROM_G, int NW, int W>
+struct GmColumnsMW {
+  __device__ static __forceinline__ bool run(const double2* Mf, double2* Lf, double* xb) {
+    const bool b = gm_column_mw<NT, CNT, FROM_G, NW, W>(Mf, Lf, xb);
+    return GmColumnsMW<NT, CNT - 1, FROM_G, NW, W>::run(Mf, Lf, xb) || b;
+  }
+};
+template <int NT, bool FROM_G, int NW, int W>
+struct GmColumnsMW<NT, 0, FROM_G, NW, W> {
+  __device__ static __forceinline__ bool run(const double2*, double2*, double*) { return false; }
+};
+template <int NT, bool FROM_G, int NW, int W>
+__device__ __noinline__ bool gm_factor_mw_w(const double* Mg, double* Ls, double* xb) {
+  const int lane = threadIdx.x & 31;
+  double2* Lf = reinterpret_cast<double2*>(Ls) + lane;
+  const double2* Mf = reinterpret_cast<const double2*>(Mg) + lane;
+  const bool bad = GmColumnsMW<NT, NT, FROM_G, NW, W>::run(Mf, Lf, xb);
+  return !__any_sync(0xffffffffu, bad);
+}
+// Entry for warp `w` of the CTA (every warp of the CTA must call it; only warp 0's result counts).
+template <int NT, bool FROM_G, int NW>
+__device__ __forceinline__ bool gm_factor_mw(const double* Mg, double* Ls, double* xb, int w) {
+  if (NW >= 2 && w == 1) return gm_factor_mw_w<NT, FROM_G, NW, (NW >= 2 ? 1 : 0)>(Mg, Ls, xb);
+  if (NW >= 4 && w == 2) return gm_factor_mw_w<NT, FROM_G, NW, (NW >= 4 ? 2 : 0)>(Mg, Ls, xb);
+  if (NW >= 4 && w == 3) return gm_factor_mw_w<NT, FROM_G, NW, (NW >= 4 ? 3 : 0)>(Mg, Ls, xb);
+  return gm_factor_mw_w<NT, FROM_G, NW, 0>(Mg, Ls, xb);
+}
+// Job mailbox of the CTA: 0 exit, 1 factor from the L2 workspace, 2 factor in place.
+__device__ __forceinline__ int* tile_job() {
+  __shared__ int job;
+  return &job;
+}
+// What warp 0 calls in place of gm_factor.
+template <int NT, int NW, bool FROM_G>
+__device__ __forceinline__ bool tile_factor(const double* Mg, double* Ls, double* xb) {
+  if (NW == 1) return gm_factor<NT, FROM_G>(Mg, Ls, xb);
+  if ((threadIdx.x & 31) == 0) *tile_job() = FROM_G ? 1 : 2;
+  __syncthreads();  // releases the helper warps; also publishes warp 0's writes of M
+  const bool ok = gm_factor_mw<NT, FROM_G, NW>(Mg, Ls, xb, 0);
+  __syncwarp();
+  return ok;
+}
+// Helper warps (1 .. NW-1) live here until warp 0 posts job 0.
+template <int NT, int NW>
+__device__ __forceinline__ void tile_helper_loop(const double* Mg, double* Ls, double* xb) {
+  const int w = threadIdx.x >> 5;
+  for (;;) {
+    __syncthreads();
+    const int job = *tile_job();
+    if (job == 0) return;
+    if (job == 1) gm_factor_mw<NT, true, NW>(Mg, Ls, xb, w);
+    else gm_factor_mw<NT, false, NW>(Mg, Ls, xb, w);
+  }
+}
+
 // Solve L L' x = b in place on the (8 NT)-vector x in shared memory.  Row-oriented block
 // substitution in t-layout; the solved blocks are read back from x itself (every lane re-reads the
 // pair it wrote, so no barrier is needed inside).  Caller syncs before and after.

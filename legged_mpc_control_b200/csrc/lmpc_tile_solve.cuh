@@ -66,7 +66,7 @@ __device__ __forceinline__ void blk_store(double* Hg, int b, const double* v) {
   __stcg(Hg + G::hoff(r + 2, r + 1), v[4]); __stcg(Hg + G::hoff(r + 1, r + 2), v[4]);
 }
 
-template <int NT>
+template <int NT, int NW = 1>
 __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws, const TilePlan& pl,
                                unsigned char* smem, double* Hg, int pi) {
   using G = TileGeom<NT>;
@@ -406,7 +406,7 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
         for (int a = 0; a < 3; ++a) dua[3 * b + a] = -(hu[3 * b + a] + gs[3 * b + a]);
       }
       __syncwarp();
-      if (!gm_factor<NT, true>(Hg, Ls, xb)) { ipm_broken = true; break; }
+      if (!tile_factor<NT, NW, true>(Hg, Ls, xb)) { ipm_broken = true; break; }
       gm_solve<NT>(Ls, dua);
       __syncwarp();
       double tau = 0.0;
@@ -601,7 +601,7 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
         du[3 * b + 2] = (apex || top) ? 0.0 : -gzt;
       }
       __syncwarp();
-      if (!gm_factor<NT, false>(Hg, Ls, xb)) break;
+      if (!tile_factor<NT, NW, false>(Hg, Ls, xb)) break;
       gm_solve<NT>(Ls, du);
       for (int i = lane; i < N; i += 32) dua[i] = 0.0;
       __syncwarp();
