@@ -63,6 +63,10 @@ enum { LMPC_DISC_EULER = 0, LMPC_DISC_ZOH = 1 };
  * NS_TWO:   H = 2(B'LB + aK), g = 2B'L(Ax0 - xref): same minimiser, multipliers scale by 2. */
 enum { LMPC_COST_REF_HALF = 0, LMPC_COST_NS_TWO = 1 };
 enum { LMPC_PREC_F64 = 0, LMPC_PREC_F32 = 1 };
+/* IPM: feasible-start Mehrotra interior point, then the exact active-set polish (default; best for
+ * cold problems).  ACTIVE_SET: the exact active-set iteration first — from the stored faces of the
+ * previous solve of that batch index (warm start is switched on at creation), or from the
+ * all-interior face set — with the interior point as fallback; both return the same minimiser. */
 enum { LMPC_SOLVER_IPM = 0, LMPC_SOLVER_ACTIVE_SET = 1 };
 
 typedef struct lmpc_params {

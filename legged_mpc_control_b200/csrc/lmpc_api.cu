@@ -240,7 +240,7 @@ static lmpc_status validate_params(const lmpc_params* p) {
   if (p->discretisation != LMPC_DISC_EULER && p->discretisation != LMPC_DISC_ZOH) { set_err("unknown discretisation"); return LMPC_ERR_INVALID_ARG; }
   if (p->cost_scaling != LMPC_COST_REF_HALF && p->cost_scaling != LMPC_COST_NS_TWO) { set_err("unknown cost_scaling"); return LMPC_ERR_INVALID_ARG; }
   if (p->precision != LMPC_PREC_F64) { set_err("precision: only LMPC_PREC_F64 is implemented in this build"); return LMPC_ERR_INVALID_ARG; }
-  if (p->solver != LMPC_SOLVER_IPM) { set_err("solver: only LMPC_SOLVER_IPM (+ exact active-set polish) is implemented in this build"); return LMPC_ERR_INVALID_ARG; }
+  if (p->solver != LMPC_SOLVER_IPM && p->solver != LMPC_SOLVER_ACTIVE_SET) { set_err("unknown solver"); return LMPC_ERR_INVALID_ARG; }
   for (int i = 0; i < 12; ++i) {
     if (!(p->r[i] > 0)) { set_err("r weights must be > 0 (the condensed Hessian must be positive definite)"); return LMPC_ERR_INVALID_ARG; }
     if (!(p->q[i] >= 0)) { set_err("q weights must be >= 0"); return LMPC_ERR_INVALID_ARG; }
@@ -261,11 +261,17 @@ static void fill_kparams(const lmpc_params& p, KParams* k) {
   if (const char* e = getenv("LMPC_TOL0")) k->tol0 = atof(e);
   if (const char* e = getenv("LMPC_RDTOL0")) k->rdtol0 = atof(e);
   if (const char* e = getenv("LMPC_FZ0")) k->fz0 = atof(e);
-  k->try_interior = 0;
+  // ACTIVE_SET: every solve starts with the exact active-set iteration (stage 4b) — from the stored
+  // faces when the problem has a warm-start record, from the all-interior face set otherwise — and
+  // the interior point is only the fallback when its repair rounds do not verify.
+  k->try_interior = p.solver == LMPC_SOLVER_ACTIVE_SET ? 1 : 0;
   if (const char* e = getenv("LMPC_TRY_INTERIOR")) k->try_interior = atoi(e);
   for (int i = 0; i < 9; ++i) k->inertia[i] = p.inertia[i];
   for (int i = 0; i < 12; ++i) { k->q[i] = p.q[i]; k->r[i] = p.r[i]; }
 }
+
+extern "C" lmpc_status lmpc_set_warm_start(lmpc_handle* h, int32_t enable, int32_t horizon_shift);
+extern "C" void lmpc_destroy(lmpc_handle* h);
 
 extern "C" lmpc_status lmpc_create(const lmpc_params* params, int32_t max_batch, int32_t device,
                                    lmpc_handle** out) {
@@ -305,6 +311,10 @@ extern "C" lmpc_status lmpc_create(const lmpc_params* params, int32_t max_batch,
   CK(h->d_order.ensure(4 * (size_t)max_batch * sizeof(int)));
   memset(&h->last_stats, 0, sizeof(KStats));
   *out = h;
+  if (params->solver == LMPC_SOLVER_ACTIVE_SET) {  // the face records are this solver's state
+    lmpc_status ws = lmpc_set_warm_start(h, 1, 1);
+    if (ws != LMPC_OK) { lmpc_destroy(h); *out = nullptr; return ws; }
+  }
   return LMPC_OK;
 }
 

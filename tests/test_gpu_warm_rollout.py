@@ -159,3 +159,25 @@ def test_warm_equals_cold_at_headline_batch():
     assert differ <= 1e-3 * B, differ
     assert warm["factorizations"].mean() < 0.15 * cold["factorizations"].mean()
     eng.close()
+
+
+def test_active_set_solver_enum(oracle):
+    """LMPC_SOLVER_ACTIVE_SET: exact active-set iteration first (interior faces on a cold problem,
+    stored faces afterwards), interior point as fallback — same minimiser as the oracle."""
+    p = presets.preset("northstar_a1")
+    p.solver = abi.SOLVER_ACTIVE_SET
+    B = 1024
+    b = synth.make_batch(B, p.horizon, p.dt, seed=21)
+    eng = _engine(p, B)
+    got = eng.compute_grfs(b)
+    ref = oracle.solve_batch(p, b, eliminate_swing=True)
+    assert ref["failures"] == 0 and (got["status"] <= abi.PROB_OK_IPM_ONLY).all()
+    assert _rel_err(got["grf"], ref["grf"]).max() <= REL_TOL
+    assert _rel_err(got["U"], ref["U"]).max() <= REL_TOL
+    cold_hits = eng.last_warm_hits  # problems the active-set iteration solved from the interior faces alone
+    assert 0 < cold_hits < B
+    eng.set_warm_start(True, horizon_shift=0)  # same problems again (creation set the closed-loop shift of 1)
+    again = eng.compute_grfs(b)
+    assert eng.last_warm_hits > 0.99 * B and again["factorizations"].mean() < 1.2
+    assert _rel_err(again["grf"], ref["grf"]).max() <= REL_TOL
+    eng.close()
