@@ -264,6 +264,9 @@ static void fill_kparams(const lmpc_params& p, KParams* k) {
   // ACTIVE_SET: every solve starts with the exact active-set iteration (stage 4b) — from the stored
   // faces when the problem has a warm-start record, from the all-interior face set otherwise — and
   // the interior point is only the fallback when its repair rounds do not verify.
+  k->step_frac = 0.999; k->sigma_pow = 3;  // swept on the headline workload (tools/gpu_sweep2.sh): flat within 1 %, 0.999 leaves the fewest interior-point-only answers
+  if (const char* e = getenv("LMPC_STEP_FRAC")) k->step_frac = atof(e);
+  if (const char* e = getenv("LMPC_SIGMA_POW")) k->sigma_pow = atoi(e);
   k->try_interior = p.solver == LMPC_SOLVER_ACTIVE_SET ? 1 : 0;
   if (const char* e = getenv("LMPC_TRY_INTERIOR")) k->try_interior = atoi(e);
   for (int i = 0; i < 9; ++i) k->inertia[i] = p.inertia[i];

@@ -468,7 +468,7 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
         }
       }
       tau2 = wmax(tau2);
-      const double alpha = tau2 > 0.995 ? 0.995 * frcp(tau2) : 1.0;
+      const double alpha = tau2 > P.step_frac ? P.step_frac * frcp(tau2) : 1.0;
       for (int b = lane; b < nb; b += 32) {
         double w[5], wb[5], d3[3];
 #pragma unroll

@@ -109,7 +109,6 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
   double* Ls = sd + pl.oLS;
   double* u = sd + pl.oU;
   double* gs = sd + pl.oGS;
-  double* z = sd + pl.oZ;
   double* prm = sd + pl.oPRM;
   double* hu = sd + pl.oHU;
   double* rd = sd + pl.oRD;
@@ -483,7 +482,7 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
           szaff = fma(s[r] * zr[r], fma(amax, q[r], 1.0) * (1.0 - amax * (1.0 + q[r])), szaff);
       szaff = wsum(szaff);
       const double rat = szaff * frcp(sz);
-      const double smu = rat * rat * rat * mub;  // sigma * mu
+      const double smu = (P.sigma_pow == 2 ? rat * rat : (P.sigma_pow == 4 ? rat * rat * rat * rat : rat * rat * rat)) * mub;  // sigma * mu
       // corrector: rhs = -rd - C'((sigma mu - ds_aff dz_aff - s z)/s)
       double w2[5], rhs[3] = {0.0, 0.0, 0.0};
       if (act) {
@@ -513,7 +512,7 @@ __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws
         }
       }
       tau2 = wmax(tau2);
-      const double alpha = tau2 > 0.995 ? 0.995 * frcp(tau2) : 1.0;
+      const double alpha = tau2 > P.step_frac ? P.step_frac * frcp(tau2) : 1.0;
       if (act) {
 #pragma unroll
         for (int r = 0; r < 5; ++r) zr[r] = fma(alpha, dz[r], zr[r]);
