@@ -4,11 +4,60 @@
 //   argv[1] = "adapter": standing A1 through ConvexMpcB200::update -> prints the 12 GRFs
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
+#include <fstream>
+#include <vector>
 
 #include "lmpc_legged_adapter.hpp"
 
+// argv: shard <in.bin> <out.bin> <preset> <n_shards>: solve the batch of in.bin (int32 B, int32 H, then x0,
+// rot, foot_pos_abs, cmd as doubles and contact as bytes) through lmpc::ShardedEngine; shards sit
+// on distinct GPUs when the box has them, otherwise all on device 0.  Writes grf [B][12] + status [B].
+static int run_shard(char** argv) {
+  std::ifstream f(argv[2], std::ios::binary);
+  std::int32_t B = 0, H = 0;
+  f.read(reinterpret_cast<char*>(&B), 4);
+  f.read(reinterpret_cast<char*>(&H), 4);
+  std::vector<double> x0(12 * B), rot(9 * B), foot(12 * B), cmd(9 * B), grf(12 * B);
+  std::vector<std::uint8_t> contact((size_t)4 * H * B);
+  std::vector<std::int32_t> status(B, -1);
+  f.read(reinterpret_cast<char*>(x0.data()), 8 * x0.size());
+  f.read(reinterpret_cast<char*>(rot.data()), 8 * rot.size());
+  f.read(reinterpret_cast<char*>(foot.data()), 8 * foot.size());
+  f.read(reinterpret_cast<char*>(cmd.data()), 8 * cmd.size());
+  f.read(reinterpret_cast<char*>(contact.data()), contact.size());
+  if (!f) { std::printf("short input file\n"); return 2; }
+  const int G = std::atoi(argv[5]);
+  try {
+    lmpc::ConvexMpcEngine probe(lmpc::preset(argv[4]), 1, 0);  // throws without a GPU
+    std::vector<int> devs;
+    for (int g = 0; g < G; ++g) {
+      int d = g;
+      try { lmpc::ConvexMpcEngine e(lmpc::preset(argv[4]), 1, d); } catch (const lmpc::Error&) { d = 0; }
+      devs.push_back(d);
+    }
+    lmpc::ShardedEngine eng(lmpc::preset(argv[4]), B, devs);
+    lmpc_batch_in in{};
+    lmpc_batch_out out{};
+    in.x0 = x0.data(); in.rot = rot.data(); in.foot_pos_abs = foot.data(); in.cmd = cmd.data(); in.contact = contact.data();
+    out.grf = grf.data(); out.status = status.data();
+    const int bad = eng.solve(B, in, out);
+    std::ofstream o(argv[3], std::ios::binary);
+    o.write(reinterpret_cast<const char*>(grf.data()), 8 * grf.size());
+    o.write(reinterpret_cast<const char*>(status.data()), 4 * status.size());
+    std::printf("shards %d devices", eng.shards());
+    for (int d : devs) std::printf(" %d", d);
+    std::printf(" unconverged_shards %d\n", bad);
+    return 0;
+  } catch (const lmpc::Error& e) {
+    std::printf("lmpc::Error %d: %s\n", (int)e.code(), e.what());
+    return e.code() == LMPC_ERR_NO_DEVICE ? 3 : 2;
+  }
+}
+
 int main(int argc, char** argv) {
+  if (argc >= 6 && !std::strcmp(argv[1], "shard")) return run_shard(argv);
   legged::LeggedState s;
   const double q[12] = {60.0, 100.0, 0.0, 0.0, 0.0, 450.0, 0.15, 0.15, 100.0, 3.0, 3.0, 5.0};
   for (int i = 0; i < 12; ++i) { s.param.q_weights[i] = q[i]; s.param.r_weights[i] = 1e-4; }

@@ -19,7 +19,7 @@ def wrapper_exe(lmpc_lib, tmp_path_factory):
     libdir = os.path.join(ROOT, "legged_mpc_control_b200")
     cmd = ["g++", "-std=c++17", "-O1", "-Wall", "-Werror", f"-I{ROOT}/include", f"-I{ROOT}/tests/cpp/mock_reference",
            f"{ROOT}/tests/cpp/test_wrapper.cpp", "-o", exe, f"-L{libdir}", "-llmpc", f"-Wl,-rpath,{libdir}",
-           "-L/usr/local/cuda/lib64", "-Wl,-rpath,/usr/local/cuda/lib64"]
+           "-L/usr/local/cuda/lib64", "-Wl,-rpath,/usr/local/cuda/lib64", "-pthread"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     assert r.returncode == 0, r.stderr
     return exe
@@ -57,3 +57,29 @@ def test_adapter_update_matches_oracle(wrapper_exe, oracle):
     assert ref["failures"] == 0
     assert np.abs(got - ref["grf"][0]).max() <= 1e-6 * max(1.0, np.abs(ref["grf"]).max())
     assert got[3:9].tolist() == [0.0] * 6  # swing legs
+
+
+@pytest.mark.gpu
+def test_sharded_engine_matches_oracle(wrapper_exe, oracle, tmp_path):
+    """lmpc::ShardedEngine (one engine + host thread per shard, contiguous index ranges, results in
+    disjoint slices of one output array): 3 shards over a ragged batch of 1001 problems."""
+    from legged_mpc_control_b200 import synth
+    p = presets.preset("northstar_a1")
+    B, H = 1001, p.horizon
+    b = synth.make_batch(B, H, p.dt, seed=31, gaits=(abi.GAIT_TROT, abi.GAIT_PRONK, abi.GAIT_STAND))
+    fin, fout = tmp_path / "in.bin", tmp_path / "out.bin"
+    with open(fin, "wb") as f:
+        f.write(np.array([B, H], np.int32).tobytes())
+        for k in ("x0", "rot", "foot_pos_abs", "cmd"):
+            f.write(np.ascontiguousarray(b[k], np.float64).tobytes())
+        f.write(np.ascontiguousarray(b["contact"], np.uint8).tobytes())
+    r = subprocess.run([wrapper_exe, "shard", str(fin), str(fout), "northstar_a1", "3"], capture_output=True, text=True)
+    assert r.returncode == 0, (r.returncode, r.stdout, r.stderr)
+    assert "shards 3" in r.stdout
+    raw = open(fout, "rb").read()
+    grf = np.frombuffer(raw[:B * 96], np.float64).reshape(B, 12)
+    status = np.frombuffer(raw[B * 96:], np.int32)
+    ref = oracle.solve_batch(p, b, eliminate_swing=True)
+    assert ref["failures"] == 0 and (status >= 0).all() and (status <= abi.PROB_OK_IPM_ONLY).all()
+    scale = np.maximum(1.0, np.abs(ref["grf"]).max(axis=1))
+    assert (np.abs(grf - ref["grf"]).max(axis=1) / scale).max() <= 1e-6
