@@ -383,6 +383,44 @@ def run_rollout(args):
         dist.destroy_process_group()
 
 
+def run_c1(args):
+    """BASELINE config 1: ONE robot, one tick (the reference's own use: ConvexMpc::grf_update at
+    100 Hz).  p50 latency of the blocking host-pointer call for both presets, cold and warm, next
+    to the oracle's single-thread time for the same problem."""
+    from legged_mpc_control_b200.engine import ConvexMpcEngine
+    from oracle import binding as ob
+    res = {}
+    for name in ("northstar_a1", "reference_a1"):
+        p = presets.preset(name)
+        b = synth.make_batch(1, p.horizon, p.dt, seed=1)
+        b = {k: b[k] for k in ("x0", "rot", "foot_pos_abs", "cmd", "contact")}
+        eng = ConvexMpcEngine(p, 1, device=0)
+        row = {}
+        for mode in ("cold", "warm"):
+            eng.set_warm_start(mode == "warm", 0)
+            for _ in range(20):
+                eng.compute_grfs(b, want_U=False, copy=False)
+            lat, kms = [], []
+            for _ in range(200):
+                t0 = time.perf_counter()
+                out = eng.compute_grfs(b, want_U=False, copy=False)
+                lat.append(time.perf_counter() - t0)
+                kms.append(eng.last_kernel_ms)
+            row[mode] = {"p50_call_us": 1e6 * float(np.median(lat)), "p95_call_us": 1e6 * float(np.percentile(lat, 95)),
+                         "p50_kernel_us": 1e3 * float(np.median(kms)), "status": int(out["status"][0]),
+                         "factorizations": int(out["iters"][0] & 0xFFFF)}
+        t0 = time.perf_counter()
+        for _ in range(20):
+            ob.solve_batch(p, b, eliminate_swing=True, nthreads=1, want_kkt=False)
+        row["cpu_oracle_us"] = 1e6 * (time.perf_counter() - t0) / 20
+        res[name] = row
+        eng.close()
+    print(json.dumps({"metric": "single_robot_tick_latency", "unit": "us", "value": res["reference_a1"]["warm"]["p50_call_us"],
+                      "higher_is_better": False, "n_gpus": 1, "dtype": "f64", "data": "synthetic",
+                      "config": {"workload": "c1_single_solve_batch1", "api": "ConvexMpcEngine.compute_grfs -> lmpc_solve (host pointers)"},
+                      "presets": res}), flush=True)
+
+
 def _ncu_traffic():
     """dram__bytes_read.sum + dram__bytes_write.sum of one solve_warp_kernel launch of the headline
     workload, from the committed `ncu --set full` capture (bench.py never runs under a profiler)."""
@@ -414,7 +452,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=BATCH)
     ap.add_argument("--no-warm", action="store_true", help="skip the warm-started re-solve measurement")
-    ap.add_argument("--workload", default="headline", choices=["headline", "c3", "ref_h30", "sweep", "rollout"],
+    ap.add_argument("--workload", default="headline", choices=["headline", "c1", "c3", "ref_h30", "sweep", "rollout"],
                     help="headline: the metric's config (default); c3 / sweep: BASELINE configs 3 / 4; ref_h30: the reference's own "
                          "H=30 preset; rollout: config 5 (16384 robots x --rollout-steps control steps, closed loop on device)")
     ap.add_argument("--rollout-steps", type=int, default=1000)
@@ -423,12 +461,14 @@ def main():
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = 3  # timing rule: W >= 3
     global _WL
-    if args.workload != "rollout":
+    if args.workload not in ("rollout", "c1"):
         _WL = args.workload
     if args.impl == "reference":
         run_reference(args)
     elif args.workload == "rollout":
         run_rollout(args)
+    elif args.workload == "c1":
+        run_c1(args)
     else:
         run_b200(args)
 
