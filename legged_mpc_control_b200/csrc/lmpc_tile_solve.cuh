@@ -36,7 +36,7 @@ __host__ __device__ inline TilePlan make_tile_plan(int H) {
   p.oQ = o; o += 5 * G::NBMAX;
   p.oIS = o; o += 5 * G::NBMAX + (G::NBMAX & 1);
   p.oPRM = o; o += 32;
-  p.oXB = o; o += 32;
+  p.oXB = o; o += 64;
   p.n_doubles = o;
   int b = o * 8;
   p.oBLK = b; b += 2 * G::NBMAX;

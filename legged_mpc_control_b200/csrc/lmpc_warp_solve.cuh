@@ -33,7 +33,7 @@ __host__ __device__ inline WarpPlan make_warp_plan(int H) {
   p.oWROW = o; o += 3 * WN;
   p.oZ = o; o += 112;
   p.oPRM = o; o += 32;
-  p.oXB = o; o += 32;
+  p.oXB = o; o += 64;
   p.n_doubles = o;
   int b = o * 8;
   p.oBLK = b; b += 2 * 24;

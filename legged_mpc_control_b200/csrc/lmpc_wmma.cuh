@@ -151,69 +151,66 @@ __device__ __forceinline__ double2 tile_ld_t(const double* tile, int g, int t) {
   return make_double2(p[0], p[8]);
 }
 
-// Factor the SPD 8x8 tile A (C-layout, full symmetric) and return inv(L) (lower triangular,
-// C-layout).  Row elimination: row g -= (A[g][c]/d_c) * row c, applied to A and to E = I, gives
-// E = inv(L_unit); inv(L) = diag(1/sqrt(d)) E.  The pivot row travels through a 2 x 16-double
-// shared-memory buffer `xb` (A row | E row, double-buffered by column parity): one predicated
-// 128-bit store pair and four broadcast loads per column instead of twelve 32-bit shuffles.  The
-// trailing matrix stays symmetric, so A[g][c] is read as A[c][g] from the same row.  A
-// non-positive pivot poisons the result with NaN.
-__device__ __noinline__ double2 wm_diag8(double ax, double ay, double* xb) {
+// Factor the SPD 8x8 tile A (C-layout, full symmetric) and return G = inv(L) (lower triangular,
+// C-layout; G A G' = I).  Elimination by 2x2 BLOCK pivots (rows 2s, 2s+1 at step s = 0, 1, 2):
+//   rows g > 2s+1:  row_g -= [A[g][2s] A[g][2s+1]] inv(P_s) [row_2s; row_2s+1],   P_s = A[2s..2s+1][2s..2s+1],
+// applied to A and to E = I, gives E = inv(L_b) of the block factorization A = L_b D_b L_b'; then
+// G = blockdiag(inv chol(P_s)) E.  Two pivots cost ONE reciprocal (of det P_s) on the sequential
+// chain instead of two, and the four 2x2 Cholesky inverses (two rsqrt each) run side by side at
+// the end.  The pivot rows travel through the shared-memory buffer `xb` (64 doubles: per row the A
+// part then the E part, two rows per step, double-buffered by step parity); the trailing matrix
+// stays symmetric, so A[g][c] is read as A[c][g] from the broadcast row.  A non-positive pivot
+// block poisons its rows with NaN.
+template <bool UNROLL>
+__device__ __forceinline__ double2 wm_diag8_impl(double ax, double ay, double* xb) {
   const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   double ex = (g == 2 * t) ? 1.0 : 0.0, ey = (g == 2 * t + 1) ? 1.0 : 0.0;
   double2* xs = reinterpret_cast<double2*>(xb) + t;   // this lane's column pair inside a row
   const double* xg = xb + g;
-#pragma unroll 1
-  for (int c = 0; c < 7; ++c) {
-    const int o = 16 * (c & 1);
-    if (g == c) {
-      xs[o / 2] = make_double2(ax, ay);
-      xs[o / 2 + 4] = make_double2(ex, ey);
+#pragma unroll(UNROLL ? 3 : 1)
+  for (int s = 0; s < 3; ++s) {
+    const int c = 2 * s;
+    const int o = 32 * (s & 1);        // doubles: row c at o (A) / o+8 (E), row c+1 at o+16 / o+24
+    if ((g >> 1) == s) {
+      const int q = (o >> 1) + 8 * (g & 1);
+      xs[q] = make_double2(ax, ay);
+      xs[q + 4] = make_double2(ex, ey);
     }
     __syncwarp();
-    const double rd_ = frcp(xb[o + c]);
-    double m = xg[o] * rd_;
-    const double2 r = xs[o / 2];
-    const double2 f = xs[o / 2 + 4];
-    m = (g > c) ? m : 0.0;
-    ax = fma(-m, r.x, ax); ay = fma(-m, r.y, ay);
-    ex = fma(-m, f.x, ex); ey = fma(-m, f.y, ey);
+    const double2 ab = *reinterpret_cast<const double2*>(xb + o + c);            // A[c][c], A[c][c+1]
+    const double cc = xb[o + 16 + c + 1];                                        // A[c+1][c+1]
+    const double rdet = frcp(fma(ab.x, cc, -ab.y * ab.y));
+    const double p0 = xg[o], p1 = xg[o + 16];                                    // A[g][c], A[g][c+1]
+    double m0 = fma(p0, cc, -p1 * ab.y) * rdet;
+    double m1 = fma(p1, ab.x, -p0 * ab.y) * rdet;
+    const bool below = g > c + 1;
+    m0 = below ? m0 : 0.0;
+    m1 = below ? m1 : 0.0;
+    const double2 r0 = xs[o >> 1], f0 = xs[(o >> 1) + 4], r1 = xs[(o >> 1) + 8], f1 = xs[(o >> 1) + 12];
+    ax = fma(-m1, r1.x, fma(-m0, r0.x, ax)); ay = fma(-m1, r1.y, fma(-m0, r0.y, ay));
+    ex = fma(-m1, f1.x, fma(-m0, f0.x, ex)); ey = fma(-m1, f1.y, fma(-m0, f0.y, ey));
   }
-  // row g is final after step g-1, so its pivot d_g = A[g][g] sits in lane (g, g>>1): fetch it
-  const double dsel = (g & 1) ? ay : ax;
-  const double dg = __shfl_sync(0xffffffffu, dsel, (lane & 28) | (g >> 1));
-  const double rs = (dg > 0.0) ? frsqrt(dg) : __longlong_as_double(0x7ff8000000000000ll);
-  return make_double2(rs * ex, rs * ey);
-}
-
-// Same, fully unrolled (used where few warps share an SM and the instruction cache is no concern).
-__device__ __noinline__ double2 wm_diag8u(double ax, double ay, double* xb) {
-  const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
-  double ex = (g == 2 * t) ? 1.0 : 0.0, ey = (g == 2 * t + 1) ? 1.0 : 0.0;
-  double2* xs = reinterpret_cast<double2*>(xb) + t;   // this lane's column pair inside a row
-  const double* xg = xb + g;
-#pragma unroll
-  for (int c = 0; c < 7; ++c) {
-    const int o = 16 * (c & 1);
-    if (g == c) {
-      xs[o / 2] = make_double2(ax, ay);
-      xs[o / 2 + 4] = make_double2(ex, ey);
-    }
-    __syncwarp();
-    const double rd_ = frcp(xb[o + c]);
-    double m = xg[o] * rd_;
-    const double2 r = xs[o / 2];
-    const double2 f = xs[o / 2 + 4];
-    m = (g > c) ? m : 0.0;
-    ax = fma(-m, r.x, ax); ay = fma(-m, r.y, ay);
-    ex = fma(-m, f.x, ex); ey = fma(-m, f.y, ey);
+  // 2x2 Cholesky inverse of every pivot block: rows 2s, 2s+1 are final after step s-1.
+  //   a = A[2s][2s], b = A[2s][2s+1] sit in lane (g = 2s, t = s); d = A[2s+1][2s+1] in lane (2s+1, s).y
+  const int sb = g >> 1, top = 8 * sb + sb;          // lane (2 sb, sb)
+  const double a = __shfl_sync(0xffffffffu, ax, top);
+  const double bq = __shfl_sync(0xffffffffu, ay, top);
+  const double d = __shfl_sync(0xffffffffu, ay, top + 4);
+  const double ux = __shfl_up_sync(0xffffffffu, ex, 4), uy = __shfl_up_sync(0xffffffffu, ey, 4);  // E row above
+  const double nan_ = __longlong_as_double(0x7ff8000000000000ll);
+  const double ra = (a > 0.0) ? frsqrt(a) : nan_;    // 1 / l11
+  const double ia = ra * ra;                         // 1 / a
+  const double sc = fma(-bq * ia, bq, d);            // l22^2 = d - b^2 / a
+  const double rs = (sc > 0.0) ? frsqrt(sc) : nan_;  // 1 / l22
+  if (g & 1) {
+    const double k = bq * ia;                        // l21 / l11
+    return make_double2(rs * fma(-k, ux, ex), rs * fma(-k, uy, ey));
   }
-  // row g is final after step g-1, so its pivot d_g = A[g][g] sits in lane (g, g>>1): fetch it
-  const double dsel = (g & 1) ? ay : ax;
-  const double dg = __shfl_sync(0xffffffffu, dsel, (lane & 28) | (g >> 1));
-  const double rs = (dg > 0.0) ? frsqrt(dg) : __longlong_as_double(0x7ff8000000000000ll);
-  return make_double2(rs * ex, rs * ey);
+  return make_double2(ra * ex, ra * ey);
 }
+// rolled (hot loop stays small in the instruction cache) and unrolled variants
+__device__ __noinline__ double2 wm_diag8(double ax, double ay, double* xb) { return wm_diag8_impl<true>(ax, ay, xb); }
+__device__ __noinline__ double2 wm_diag8u(double ax, double ay, double* xb) { return wm_diag8_impl<true>(ax, ay, xb); }
 
 // Factor M = L L' (64 x 64, 8 x 8 tiles).  FROM_G: the lower tiles of M are read from the
 // full-symmetric fragment-ordered workspace Mg in global memory (L2; the interior-point loop keeps
