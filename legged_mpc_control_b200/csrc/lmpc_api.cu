@@ -188,6 +188,7 @@ extern "C" int32_t lmpc_abi_version(void) { return LMPC_ABI_VERSION; }
     }                                                                                         \
   } while (0)
 
+static constexpr int kPackMax = 64;  // batches up to this size take the packed host path
 static constexpr int kThreads = 64;
 static constexpr int kThreadsSpill = 256;
 static constexpr int kTileWarpsA = 1, kTileWarpsB = 4;  // measured: NT=15 gains nothing from helpers (581k vs 587k/445k solves/s at 2/4 warps), NT=24 +31% at 4
@@ -221,6 +222,10 @@ struct lmpc_handle {
   DevBuf d_stats, d_counter, d_ws, d_wsA, d_wsT1, d_wsT2, d_order, d_warm;
   bool warm_enabled = false;
   int warm_shift = 1;
+  // small-batch host path: one packed H2D and one packed D2H (a single robot's tick is latency-bound)
+  DevBuf d_pin, d_pout;
+  unsigned char* h_pin = nullptr;
+  unsigned char* h_pout = nullptr;
   // closed-loop rollout state (lmpc_rollout)
   DevBuf d_rx, d_rfw, d_rph, d_rgait, d_rspeed, d_rtot, d_xlog, d_glog;
   cudaEvent_t ev_r0 = nullptr, ev_r1 = nullptr;
@@ -328,7 +333,7 @@ extern "C" void lmpc_destroy(lmpc_handle* h) {
   DevBuf* bufs[] = {&h->d_x0, &h->d_rot, &h->d_foot, &h->d_cmd, &h->d_contact, &h->d_q, &h->d_r, &h->d_mu,
                     &h->d_fz, &h->d_mass, &h->d_inertia, &h->d_grf, &h->d_status, &h->d_iters, &h->d_active,
                     &h->d_U, &h->d_stats, &h->d_counter, &h->d_ws, &h->d_wsA, &h->d_wsT1, &h->d_wsT2, &h->d_order, &h->d_warm,
-                    &h->d_rx, &h->d_rfw, &h->d_rph, &h->d_rgait, &h->d_rspeed, &h->d_rtot, &h->d_xlog, &h->d_glog};
+                    &h->d_pin, &h->d_pout, &h->d_rx, &h->d_rfw, &h->d_rph, &h->d_rgait, &h->d_rspeed, &h->d_rtot, &h->d_xlog, &h->d_glog};
   for (DevBuf* b : bufs) b->release();
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
@@ -336,6 +341,8 @@ extern "C" void lmpc_destroy(lmpc_handle* h) {
   if (h->ev_r0) cudaEventDestroy(h->ev_r0);
   if (h->ev_r1) cudaEventDestroy(h->ev_r1);
   if (h->h_cls) cudaFreeHost(h->h_cls);
+  if (h->h_pin) cudaFreeHost(h->h_pin);
+  if (h->h_pout) cudaFreeHost(h->h_pout);
   if (h->stream) cudaStreamDestroy(h->stream);
   delete h;
 }
@@ -529,6 +536,56 @@ extern "C" lmpc_status lmpc_solve(lmpc_handle* h, int32_t batch, const lmpc_batc
     st = launch_solve(h, device_batch(in, out, batch), s);
     if (st != LMPC_OK) return st;
     return finish_solve(h, s);
+  }
+  // ---- small batch, plain inputs: pack -> one H2D -> kernels -> one D2H -> unpack (saves ~8 driver
+  //      calls; the reference's own use is ONE robot per tick)
+  if (batch <= kPackMax && !in->q && !in->r && !in->mu && !in->fz_max && !in->mass && !in->inertia && !out->U) {
+    const int Hh = h->kp.H, Wd = LMPC_ACTIVE_WORDS(Hh);
+    const size_t nb = (size_t)batch;
+    const size_t o_rot = nb * 96, o_foot = o_rot + nb * 72, o_cmd = o_foot + nb * 96, o_con = o_cmd + nb * 72;
+    const size_t in_bytes = o_con + ((nb * 4 * Hh + 7) & ~(size_t)7);
+    const size_t p_grf = (sizeof(KStats) + 15) & ~(size_t)15, p_st = p_grf + nb * 96, p_it = p_st + nb * 4, p_act = p_it + nb * 4;
+    const size_t out_bytes = p_act + nb * 4 * Wd;
+    if (!h->h_pin) {
+      const size_t cap_in = (size_t)kPackMax * (96 + 72 + 96 + 72 + 4 * LMPC_MAX_HORIZON) + 64;
+      const size_t cap_out = 64 + sizeof(KStats) + (size_t)kPackMax * (96 + 8 + 4 * LMPC_ACTIVE_WORDS(LMPC_MAX_HORIZON));
+      CK(cudaMallocHost((void**)&h->h_pin, cap_in));
+      CK(cudaMallocHost((void**)&h->h_pout, cap_out));
+      CK(h->d_pin.ensure(cap_in));
+      CK(h->d_pout.ensure(cap_out));
+    }
+    memcpy(h->h_pin, in->x0, nb * 96);
+    memcpy(h->h_pin + o_rot, in->rot, nb * 72);
+    memcpy(h->h_pin + o_foot, in->foot_pos_abs, nb * 96);
+    memcpy(h->h_pin + o_cmd, in->cmd, nb * 72);
+    memcpy(h->h_pin + o_con, in->contact, nb * 4 * Hh);
+    CK(cudaMemcpyAsync(h->d_pin.p, h->h_pin, in_bytes, cudaMemcpyHostToDevice, s));
+    unsigned char* di = (unsigned char*)h->d_pin.p;
+    unsigned char* dout = (unsigned char*)h->d_pout.p;
+    KBatch kb;
+    memset(&kb, 0, sizeof(kb));
+    kb.x0 = (const double*)di; kb.rot = (const double*)(di + o_rot); kb.foot = (const double*)(di + o_foot);
+    kb.cmd = (const double*)(di + o_cmd); kb.contact = di + o_con;
+    kb.grf = (double*)(dout + p_grf); kb.status = (int*)(dout + p_st); kb.iters = (int*)(dout + p_it);
+    kb.active = (uint32_t*)(dout + p_act); kb.B = batch;
+    void* saved = h->d_stats.p;  // the statistics block rides at the head of the packed output
+    h->d_stats.p = dout;
+    st = launch_solve(h, kb, s);
+    h->d_stats.p = saved;
+    if (st != LMPC_OK) return st;
+    CK(cudaMemcpyAsync(h->h_pout, dout, out_bytes, cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    memcpy(&h->last_stats, h->h_pout, sizeof(KStats));
+    memcpy(out->grf, h->h_pout + p_grf, nb * 96);
+    if (out->status) memcpy(out->status, h->h_pout + p_st, nb * 4);
+    if (out->iters) memcpy(out->iters, h->h_pout + p_it, nb * 4);
+    if (out->active_set) memcpy(out->active_set, h->h_pout + p_act, nb * 4 * Wd);
+    CK(cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1));
+    if (h->last_stats.not_ok > 0) {
+      set_err(std::to_string((unsigned long long)h->last_stats.not_ok) + " problem(s) did not converge (grf zeroed)");
+      return LMPC_ERR_NOT_CONVERGED;
+    }
+    return LMPC_OK;
   }
   // host pointers: stage through device buffers owned by the handle
   const int H = h->kp.H;
