@@ -97,7 +97,7 @@ def run_reference(args):
     sample = ""
     cores = os.cpu_count() or 1
     for i in range(args.warmup + args.steps):
-        v, cores, sample = cpu_sample(p, seconds_target=max(2.0, 60.0 / (args.warmup + args.steps)))
+        v, cores, sample = cpu_sample(p, seconds_target=args.cpu_seconds or max(2.0, 60.0 / (args.warmup + args.steps)))
         if i >= args.warmup:
             vals.append(v)
     val = float(np.mean(vals))
@@ -305,7 +305,7 @@ def run_b200(args):
             "roofline": {
                 "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
                 "traffic": _ncu_traffic() if _WL == "headline" else None,
-                "traffic_source": "profiles/r01_v10_ncu_full_solve_warp_kernel.csv (bytes per launch; input reads + write-backs of the L2-resident "
+                "traffic_source": "profiles/r01_v12_ncu_full_solve_warp_kernel.csv (bytes per launch; input reads + write-backs of the L2-resident "
                                   "Hessian workspace, <0.1% of HBM peak: the bound is FP64 latency, not DRAM)",
                 "kernel": "lmpc::solve_warp_kernel" if stats["mean_n_eff"] <= 63 else "lmpc::solve_tile_kernel / solve_kernel (by size class)",
                 "kernel_ms": kms,
@@ -424,7 +424,7 @@ def run_c1(args):
 def _ncu_traffic():
     """dram__bytes_read.sum + dram__bytes_write.sum of one solve_warp_kernel launch of the headline
     workload, from the committed `ncu --set full` capture (bench.py never runs under a profiler)."""
-    path = os.path.join(ROOT, "profiles", "r01_v10_ncu_full_solve_warp_kernel.csv")
+    path = os.path.join(ROOT, "profiles", "r01_v12_ncu_full_solve_warp_kernel.csv")
     try:
         tot = 0.0
         for ln in open(path):
@@ -451,6 +451,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=BATCH)
+    ap.add_argument("--cpu-seconds", type=float, default=None, help="CPU work per step of --impl reference (default: 60 s over the run)")
     ap.add_argument("--no-warm", action="store_true", help="skip the warm-started re-solve measurement")
     ap.add_argument("--workload", default="headline", choices=["headline", "c1", "c3", "ref_h30", "sweep", "rollout"],
                     help="headline: the metric's config (default); c3 / sweep: BASELINE configs 3 / 4; ref_h30: the reference's own "

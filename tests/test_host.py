@@ -175,3 +175,25 @@ def test_shard_and_gather_world2_gloo(tmp_path, oracle):
                        capture_output=True, text=True, env=env, timeout=300)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert "GATHER_OK" in r.stdout
+
+
+def test_bench_reference_arm_contract(oracle):
+    """`bench.py --impl reference` (the oracle port on the host cores; the reference itself cannot be
+    built here) prints ONE JSON line with the contract's keys; non-zero ranks print nothing."""
+    import json
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "0", "--cpu-seconds", "0.5"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [ln for ln in r.stdout.splitlines() if ln.strip()]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["metric"] == "convex_mpc_qp_solves_per_sec" and d["unit"] == "solves/s"
+    assert d["higher_is_better"] is True and d["value"] > 0 and d["cpu_baseline"]["kind"] == "port"
+    assert d["e2e"] == {"value": d["value"], "unit": "solves/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    assert d["config"]["workload"].startswith("a1_trot_h10")
+    env = dict(os.environ, RANK="1", WORLD_SIZE="2")
+    r1 = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=env)
+    assert r1.returncode == 0 and r1.stdout.strip() == ""
