@@ -138,11 +138,16 @@ def make_rollout_state(n: int, seed: int, robot: str = "a1", gaits=(abi.GAIT_TRO
                     np.zeros(n), np.zeros(n), f(43, -0.8, 0.8)], axis=1)
     gaits = list(gaits)
     gsel = np.minimum((u01(seed, idx, 50) * len(gaits)).astype(np.int64), len(gaits) - 1)
+    gait_arr = np.asarray(gaits, np.int32)[gsel]
+    standing = gait_arr == abi.GAIT_STAND  # feet never relocate: a standing robot is commanded to stay
+    cmd[standing, 3:6] = 0.0
+    cmd[standing, 8] = 0.0
+    x[standing, 9:11] *= 0.1
     if gait_speed is None:
         gait_speed = presets.A1_GAIT_SPEED if robot == "a1" else presets.GO1_GAIT_SPEED
     return {"x": np.ascontiguousarray(x), "foot_world": np.ascontiguousarray(fw.reshape(n, 12)),
             "phase": np.ascontiguousarray(np.repeat(u01(seed, idx, 51)[:, None], 4, axis=1)),
-            "gait": np.ascontiguousarray(np.asarray(gaits, np.int32)[gsel]),
+            "gait": np.ascontiguousarray(gait_arr),
             "gait_speed": np.full(n, float(gait_speed)), "cmd": np.ascontiguousarray(cmd),
             "foot_rel": np.ascontiguousarray(fh.reshape(12))}
 
