@@ -93,8 +93,7 @@ __global__ void __maxnreg__(255) solve_tile_kernel(const __grid_constant__ KPara
   constexpr size_t kSlot = (size_t)TileGeom<NT>::HS + 6 * TileGeom<NT>::NBMAX + 2;
   double* Hg = gws + (size_t)blockIdx.x * kSlot;
   if (NW > 1 && threadIdx.x >= 32) {
-    double* sd = reinterpret_cast<double*>(smem);
-    tile_helper_loop<NT, NW>(Hg, sd + pl.oLS, sd + pl.oXB);
+    tile_helper_loop<NT, NW>(P, pl, smem, Hg);
     return;
   }
   const int lane = threadIdx.x;

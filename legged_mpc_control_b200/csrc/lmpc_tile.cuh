@@ -164,7 +164,8 @@ __device__ __forceinline__ bool gm_factor_mw(const double* Mg, double* Ls, doubl
   if (NW >= 4 && w == 3) return gm_factor_mw_w<NT, FROM_G, NW, (NW >= 4 ? 3 : 0)>(Mg, Ls, xb);
   return gm_factor_mw_w<NT, FROM_G, NW, 0>(Mg, Ls, xb);
 }
-// Job mailbox of the CTA: 0 exit, 1 factor from the L2 workspace, 2 factor in place.
+// Job mailbox of the CTA: 0 exit, 1 factor from the L2 workspace, 2 factor in place, 3 Hessian
+// blocks, 4 reduced matrix of the polish (lmpc_tile_solve.cuh).
 __device__ __forceinline__ int* tile_job() {
   __shared__ int job;
   return &job;
@@ -179,19 +180,6 @@ __device__ __forceinline__ bool tile_factor(const double* Mg, double* Ls, double
   __syncwarp();
   return ok;
 }
-// Helper warps (1 .. NW-1) live here until warp 0 posts job 0.
-template <int NT, int NW>
-__device__ __forceinline__ void tile_helper_loop(const double* Mg, double* Ls, double* xb) {
-  const int w = threadIdx.x >> 5;
-  for (;;) {
-    __syncthreads();
-    const int job = *tile_job();
-    if (job == 0) return;
-    if (job == 1) gm_factor_mw<NT, true, NW>(Mg, Ls, xb, w);
-    else gm_factor_mw<NT, false, NW>(Mg, Ls, xb, w);
-  }
-}
-
 // Solve L L' x = b in place on the (8 NT)-vector x in shared memory.  Row-oriented block
 // substitution in t-layout; the solved blocks are read back from x itself (every lane re-reads the
 // pair it wrote, so no barrier is needed inside).  Caller syncs before and after.
@@ -243,13 +231,15 @@ __device__ __noinline__ void gm_solve(const double* Ls, double* x) {
 }
 
 // y = H x for the full-symmetric workspace (global, L2); x, y (8 NT)-vectors in shared memory.
+// Tile rows I = i0, i0 + di, ...: one warp does them all (i0 = 0, di = 1) or the warps of the CTA
+// take every NW-th row (job 5).
 template <int NT>
-__device__ __noinline__ void gm_symv(const double* Hg, const double* x, double* y) {
+__device__ __noinline__ void gm_symv(const double* Hg, const double* x, double* y, int i0 = 0, int di = 1) {
   const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   const double2* Hf = reinterpret_cast<const double2*>(Hg) + lane;
   const double2* xt = reinterpret_cast<const double2*>(x) + t;
 #pragma unroll 1
-  for (int I = 0; I < NT; ++I) {
+  for (int I = i0; I < NT; I += di) {
     double p0 = 0.0, p1 = 0.0;
     const double2* row = Hf + 32 * (I * NT);
 #pragma unroll 8

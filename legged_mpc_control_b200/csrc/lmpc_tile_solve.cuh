@@ -66,6 +66,161 @@ __device__ __forceinline__ void blk_store(double* Hg, int b, const double* v) {
   __stcg(Hg + G::hoff(r + 2, r + 1), v[4]); __stcg(Hg + G::hoff(r + 1, r + 2), v[4]);
 }
 
+// Reduced Hessian blocks (+ identity padding) into the L2 workspace, pair index strided over `nthr`
+// threads: one warp, or every warp of the CTA when helper warps exist (job 3).
+template <int NT>
+__device__ void tile_hessian_blocks(const KParams& P, const TilePlan& pl, unsigned char* smem, double* Hg, int nb, int n,
+                                    double sc, double im2, int tid, int nthr) {
+  using G = TileGeom<NT>;
+  constexpr int N = G::N;
+  const int H = P.H;
+  double* sd = reinterpret_cast<double*>(smem);
+  const double* prm = sd + pl.oPRM;
+  const double* qw = prm + PRM_Q;
+  const double* rw = prm + PRM_R;
+  const double* Bw = sd + pl.oBW;
+  const double* cosv = sd + pl.oCOS;
+  const double* sinv = sd + pl.oSIN;
+  const double* Cs = sd + pl.oCS;
+  const double* Ss = sd + pl.oSS;
+  const unsigned char* blk = smem + pl.oBLK;
+  double* Hd = Hg + G::HS;
+  const double dt2 = P.dt * P.dt, theta = P.zoh ? 0.5 : 0.0;
+  for (int idx = tid; idx < N * (N - n); idx += nthr) {  // identity padding for rows/cols >= n
+    const int c = n + idx / N, r = idx % N;
+    __stcg(Hg + G::hoff(r, c), (r == c) ? 1.0 : 0.0);
+    __stcg(Hg + G::hoff(c, r), (r == c) ? 1.0 : 0.0);
+  }
+  const int npairs = (nb * (nb + 1)) >> 1;
+  for (int pr = tid; pr < npairs; pr += nthr) {
+    int b1, b2;
+    pair_from_index(pr, b1, b2);
+    double o[9];
+    wblock(H, dt2, theta, P.cs, im2, qw, rw, Bw, cosv, sinv, Cs, Ss, blk[2 * b1], blk[2 * b1 + 1], blk[2 * b2],
+           blk[2 * b2 + 1], b1 == b2, o);
+#pragma unroll
+    for (int a1 = 0; a1 < 3; ++a1)
+#pragma unroll
+      for (int a2 = 0; a2 < 3; ++a2) {
+        const int r = 3 * b1 + a1, c = 3 * b2 + a2;
+        const double v = sc * o[a1 + 3 * a2];
+        __stcg(Hg + G::hoff(r, c), v);
+        __stcg(Hg + G::hoff(c, r), v);
+      }
+    if (b1 == b2) {  // keep the diagonal block: the interior point overwrites it with H_bb + W_b
+      double* hd = Hd + 6 * b1;
+      __stcg(hd + 0, sc * o[0]); __stcg(hd + 1, sc * o[1]); __stcg(hd + 2, sc * o[2]);
+      __stcg(hd + 3, sc * o[4]); __stcg(hd + 4, sc * o[5]); __stcg(hd + 5, sc * o[8]);
+    }
+  }
+}
+
+// Reduced matrix of the polish, Mt = T' H T with pinned rows/cols replaced by identity, from the L2
+// workspace into the factor storage; same striding (job 4).
+template <int NT>
+__device__ void tile_reduced_matrix(const TilePlan& pl, unsigned char* smem, const double* Hg, int nb, int n, double mu,
+                                    int tid, int nthr) {
+  using G = TileGeom<NT>;
+  constexpr int N = G::N;
+  double* Ls = reinterpret_cast<double*>(smem) + pl.oLS;
+  const signed char* face = reinterpret_cast<const signed char*>(smem + pl.oFACE);
+  const int npairs = (nb * (nb + 1)) >> 1;
+  for (int pr = tid; pr < npairs; pr += nthr) {
+    int b1, b2;
+    pair_from_index(pr, b1, b2);
+    double X[9];
+#pragma unroll
+    for (int a1 = 0; a1 < 3; ++a1)
+#pragma unroll
+      for (int a2 = 0; a2 < 3; ++a2) X[a1 + 3 * a2] = __ldcg(Hg + G::hoff(3 * b1 + a1, 3 * b2 + a2));
+    const double s1x = mu * face[4 * b1], s1y = mu * face[4 * b1 + 1];
+    const double s2x = mu * face[4 * b2], s2y = mu * face[4 * b2 + 1];
+#pragma unroll
+    for (int a2 = 0; a2 < 3; ++a2) X[2 + 3 * a2] += s1x * X[0 + 3 * a2] + s1y * X[1 + 3 * a2];
+#pragma unroll
+    for (int a1 = 0; a1 < 3; ++a1) X[a1 + 6] += s2x * X[a1] + s2y * X[a1 + 3];
+    const int ap1 = face[4 * b1 + 3], ap2 = face[4 * b2 + 3];
+    const bool pin1[3] = {ap1 || face[4 * b1] != 0, ap1 || face[4 * b1 + 1] != 0, ap1 || face[4 * b1 + 2] != 0};
+    const bool pin2[3] = {ap2 || face[4 * b2] != 0, ap2 || face[4 * b2 + 1] != 0, ap2 || face[4 * b2 + 2] != 0};
+#pragma unroll
+    for (int a1 = 0; a1 < 3; ++a1)
+#pragma unroll
+      for (int a2 = 0; a2 < 3; ++a2) {
+        const int r = 3 * b1 + a1, c = 3 * b2 + a2;
+        if (c <= r) {
+          double v = X[a1 + 3 * a2];
+          if (pin1[a1] || pin2[a2]) v = (r == c) ? 1.0 : 0.0;
+          Ls[G::loff(r, c)] = v;
+          if ((r >> 3) == (c >> 3)) Ls[G::loff(c, r)] = v;  // diagonal tiles are kept full
+        }
+      }
+  }
+  for (int r = n; r < N; ++r)  // identity padding rows n..N-1
+    for (int c = tid; c <= r; c += nthr) {
+      Ls[G::loff(r, c)] = (r == c) ? 1.0 : 0.0;
+      if ((r >> 3) == (c >> 3)) Ls[G::loff(c, r)] = (r == c) ? 1.0 : 0.0;
+    }
+}
+
+// Mailbox arguments of the shared jobs.
+struct TileJobArgs { int nb, n; double sc, im2, mu; const double* x; double* y; };
+__device__ __forceinline__ TileJobArgs* tile_job_args() {
+  __shared__ TileJobArgs a;
+  return &a;
+}
+// Warp 0's call: runs job 3 / 4 alone (NW = 1) or together with the helper warps.
+template <int NT, int NW>
+__device__ __forceinline__ void tile_shared(int job, const KParams& P, const TilePlan& pl, unsigned char* smem, double* Hg,
+                                            int nb, int n, double sc, double im2, double mu) {
+  if (NW == 1) {
+    if (job == 3) tile_hessian_blocks<NT>(P, pl, smem, Hg, nb, n, sc, im2, threadIdx.x & 31, 32);
+    else tile_reduced_matrix<NT>(pl, smem, Hg, nb, n, mu, threadIdx.x & 31, 32);
+    return;
+  }
+  if ((threadIdx.x & 31) == 0) {
+    TileJobArgs* a = tile_job_args();
+    a->nb = nb; a->n = n; a->sc = sc; a->im2 = im2; a->mu = mu;
+    *tile_job() = job;
+  }
+  __syncthreads();  // release the helpers (also publishes warp 0's shared-memory state)
+  if (job == 3) tile_hessian_blocks<NT>(P, pl, smem, Hg, nb, n, sc, im2, threadIdx.x, 32 * NW);
+  else tile_reduced_matrix<NT>(pl, smem, Hg, nb, n, mu, threadIdx.x, 32 * NW);
+  __syncthreads();  // every warp's share is written
+}
+// y = H x with the tile rows dealt over the warps of the CTA (job 5); x, y in shared memory.
+template <int NT, int NW>
+__device__ __forceinline__ void tile_symv(const double* Hg, const double* x, double* y) {
+  if (NW == 1) { gm_symv<NT>(Hg, x, y); return; }
+  if ((threadIdx.x & 31) == 0) {
+    TileJobArgs* a = tile_job_args();
+    a->x = x; a->y = y;
+    *tile_job() = 5;
+  }
+  __syncthreads();
+  gm_symv<NT>(Hg, x, y, 0, NW);
+  __syncthreads();
+}
+// Helper warps (1 .. NW-1) live here until warp 0 posts job 0.
+template <int NT, int NW>
+__device__ __forceinline__ void tile_helper_loop(const KParams& P, const TilePlan& pl, unsigned char* smem, double* Hg) {
+  double* sd = reinterpret_cast<double*>(smem);
+  const int w = threadIdx.x >> 5;
+  for (;;) {
+    __syncthreads();
+    const int job = *tile_job();
+    if (job == 0) return;
+    if (job == 1) gm_factor_mw<NT, true, NW>(Hg, sd + pl.oLS, sd + pl.oXB, w);
+    else if (job == 2) gm_factor_mw<NT, false, NW>(Hg, sd + pl.oLS, sd + pl.oXB, w);
+    else {
+      const TileJobArgs a = *tile_job_args();
+      if (job == 3) tile_hessian_blocks<NT>(P, pl, smem, Hg, a.nb, a.n, a.sc, a.im2, threadIdx.x, 32 * NW);
+      else if (job == 4) tile_reduced_matrix<NT>(pl, smem, Hg, a.nb, a.n, a.mu, threadIdx.x, 32 * NW);
+      else gm_symv<NT>(Hg, a.x, a.y, w, NW);
+      __syncthreads();
+    }
+  }
+}
+
 template <int NT, int NW = 1>
 __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws, const TilePlan& pl,
                                unsigned char* smem, double* Hg, int pi) {
@@ -243,33 +398,7 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
     }
     dmax = wmax(dmax);
     sc = 1.0 / dmax;
-    for (int idx = lane; idx < N * (N - n); idx += 32) {  // identity padding for rows/cols >= n
-      const int c = n + idx / N, r = idx % N;
-      __stcg(Hg + G::hoff(r, c), (r == c) ? 1.0 : 0.0);
-      __stcg(Hg + G::hoff(c, r), (r == c) ? 1.0 : 0.0);
-    }
-    const int npairs = (nb * (nb + 1)) >> 1;
-    for (int pr = lane; pr < npairs; pr += 32) {
-      int b1, b2;
-      pair_from_index(pr, b1, b2);
-      double o[9];
-      wblock(H, dt2, theta, P.cs, im2, qw, rw, Bw, cosv, sinv, Cs, Ss, blk[2 * b1], blk[2 * b1 + 1], blk[2 * b2],
-             blk[2 * b2 + 1], b1 == b2, o);
-#pragma unroll
-      for (int a1 = 0; a1 < 3; ++a1)
-#pragma unroll
-        for (int a2 = 0; a2 < 3; ++a2) {
-          const int r = 3 * b1 + a1, c = 3 * b2 + a2;
-          const double v = sc * o[a1 + 3 * a2];
-          __stcg(Hg + G::hoff(r, c), v);
-          __stcg(Hg + G::hoff(c, r), v);
-        }
-      if (b1 == b2) {  // keep the diagonal block: the interior point overwrites it with H_bb + W_b
-        double* hd = Hd + 6 * b1;
-        __stcg(hd + 0, sc * o[0]); __stcg(hd + 1, sc * o[1]); __stcg(hd + 2, sc * o[2]);
-        __stcg(hd + 3, sc * o[4]); __stcg(hd + 4, sc * o[5]); __stcg(hd + 5, sc * o[8]);
-      }
-    }
+    tile_shared<NT, NW>(3, P, pl, smem, Hg, nb, n, sc, im2, mu);
     for (int b = lane; b < nb; b += 32) {
       const int j = blk[2 * b], l = blk[2 * b + 1];
 #pragma unroll
@@ -319,7 +448,7 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
     if (stage >= 0 && !ipm_inited) {  // interior-point start (skipped entirely by a verified warm start)
       ipm_inited = true;
       {
-        gm_symv<NT>(Hg, u, hu);
+        tile_symv<NT, NW>(Hg, u, hu);
         __syncwarp();
         double gi = 0, ssum = 0;
         for (int i = lane; i < N; i += 32) gi = fmax(gi, fabs(hu[i] + gs[i]));
@@ -370,7 +499,7 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
           blk_store<NT>(Hg, b, hd);
         }
         __syncwarp();
-        gm_symv<NT>(Hg, u, hu);
+        tile_symv<NT, NW>(Hg, u, hu);
         __syncwarp();
         double ri = 0;
         for (int b = lane; b < nb; b += 32) {
@@ -545,50 +674,13 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
       }
       __syncwarp();
       if (__any_sync(0xffffffffu, pinned_top)) {
-        gm_symv<NT>(Hg, rd, hu);
+        tile_symv<NT, NW>(Hg, rd, hu);
       } else {  // p = 0: H p = 0 without reading H
         for (int i = lane; i < N; i += 32) hu[i] = 0.0;
       }
       __syncwarp();
       // Mt = T' H T with pinned rows/cols replaced by identity, written into the factor storage
-      {
-        const int npairs = (nb * (nb + 1)) >> 1;
-        for (int pr = lane; pr < npairs; pr += 32) {
-          int b1, b2;
-          pair_from_index(pr, b1, b2);
-          double X[9];
-#pragma unroll
-          for (int a1 = 0; a1 < 3; ++a1)
-#pragma unroll
-            for (int a2 = 0; a2 < 3; ++a2) X[a1 + 3 * a2] = __ldcg(Hg + G::hoff(3 * b1 + a1, 3 * b2 + a2));
-          const double s1x = mu * face[4 * b1], s1y = mu * face[4 * b1 + 1];
-          const double s2x = mu * face[4 * b2], s2y = mu * face[4 * b2 + 1];
-#pragma unroll
-          for (int a2 = 0; a2 < 3; ++a2) X[2 + 3 * a2] += s1x * X[0 + 3 * a2] + s1y * X[1 + 3 * a2];
-#pragma unroll
-          for (int a1 = 0; a1 < 3; ++a1) X[a1 + 6] += s2x * X[a1] + s2y * X[a1 + 3];
-          const int ap1 = face[4 * b1 + 3], ap2 = face[4 * b2 + 3];
-          const bool pin1[3] = {ap1 || face[4 * b1] != 0, ap1 || face[4 * b1 + 1] != 0, ap1 || face[4 * b1 + 2] != 0};
-          const bool pin2[3] = {ap2 || face[4 * b2] != 0, ap2 || face[4 * b2 + 1] != 0, ap2 || face[4 * b2 + 2] != 0};
-#pragma unroll
-          for (int a1 = 0; a1 < 3; ++a1)
-#pragma unroll
-            for (int a2 = 0; a2 < 3; ++a2) {
-              const int r = 3 * b1 + a1, c = 3 * b2 + a2;
-              if (c <= r) {
-                double v = X[a1 + 3 * a2];
-                if (pin1[a1] || pin2[a2]) v = (r == c) ? 1.0 : 0.0;
-                Ls[G::loff(r, c)] = v;
-                if ((r >> 3) == (c >> 3)) Ls[G::loff(c, r)] = v;  // diagonal tiles are kept full
-              }
-            }
-        }
-        for (int r = n; r < N; ++r)  // identity padding rows n..N-1
-          for (int c = lane; c <= r; c += 32) {
-            Ls[G::loff(r, c)] = (r == c) ? 1.0 : 0.0;
-            if ((r >> 3) == (c >> 3)) Ls[G::loff(c, r)] = (r == c) ? 1.0 : 0.0;
-          }
-      }
+      tile_shared<NT, NW>(4, P, pl, smem, Hg, nb, n, sc, im2, mu);
       __syncwarp();
       for (int i = lane; i < N; i += 32) du[i] = 0.0;
       __syncwarp();
@@ -613,7 +705,7 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
         dua[3 * b + 2] = vz + rd[3 * b + 2];
       }
       __syncwarp();
-      gm_symv<NT>(Hg, dua, hu);
+      tile_symv<NT, NW>(Hg, dua, hu);
       __syncwarp();
       int changed = 0;
       for (int b = lane; b < nb; b += 32) {
@@ -662,7 +754,7 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
       break;
     } else {
       // back to the interior point at a tighter mu: H u of the interior iterate is needed again
-      gm_symv<NT>(Hg, u, hu);
+      tile_symv<NT, NW>(Hg, u, hu);
       __syncwarp();
     }
   }
