@@ -190,7 +190,9 @@ extern "C" int32_t lmpc_abi_version(void) { return LMPC_ABI_VERSION; }
 static constexpr int kPackMax = 64;  // batches up to this size take the packed host path
 static constexpr int kThreads = 64;
 static constexpr int kThreadsSpill = 256;
-static constexpr int kTileWarpsA = 1, kTileWarpsB = 4;  // measured: NT=15 gains nothing from helpers (581k vs 587k/445k solves/s at 2/4 warps), NT=24 +31% at 4
+// Warps per QP of the tile classes, measured (C3 / reference preset, solves/s): NT=15: 598k / 647k / 519k at
+// 1 / 2 / 4 warps (4 warps cost the third CTA per SM); NT=24: 90k / 106k / 146k (one CTA per SM anyway).
+static constexpr int kTileWarpsA = 2, kTileWarpsB = 4;
 
 struct DevBuf {
   void* p = nullptr;
@@ -371,6 +373,7 @@ template <int NT>
 static lmpc_status launch_tile(lmpc_handle* h, const KBatch& kb, cudaStream_t s, DevBuf* wsbuf, int* order, int* count,
                                int* work) {
   int nw = NT == lmpc::kTileA ? kTileWarpsA : kTileWarpsB;
+  if (kb.B <= h->num_sms) nw = 4;  // fewer problems than SMs: latency counts, occupancy does not
   if (const char* e = getenv("LMPC_TILE_NW")) nw = atoi(e);
   if (nw == 1) return launch_tile_nw<NT, 1>(h, kb, s, wsbuf, order, count, work);
   if (nw == 2) return launch_tile_nw<NT, 2>(h, kb, s, wsbuf, order, count, work);
