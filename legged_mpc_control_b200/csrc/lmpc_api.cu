@@ -32,7 +32,7 @@ namespace lmpc {
 #define LMPC_WARP_MAXNREG 255
 #endif
 constexpr int kNumClasses = 4;
-constexpr int kTileA = 15, kTileB = 24;
+constexpr int kTileA = 15, kTileB = 24, kTileC = 48;  // 8 x 48 = 384 = 12 x LMPC_MAX_HORIZON
 __host__ __device__ inline int size_class(int n) {
   return n <= 3 * WNBMAX ? 0 : (n <= 8 * kTileA ? 1 : (n <= 8 * kTileB ? 2 : 3));
 }
@@ -90,7 +90,7 @@ __global__ void __maxnreg__(255) solve_tile_kernel(const __grid_constant__ KPara
                                                              int* work_counter) {
   extern __shared__ __align__(16) unsigned char smem[];
   const TilePlan pl = make_tile_plan<NT>(P.H);
-  constexpr size_t kSlot = (size_t)TileGeom<NT>::HS + 6 * TileGeom<NT>::NBMAX + 2;
+  const size_t kSlot = tile_slot_doubles<NT>();
   double* Hg = gws + (size_t)blockIdx.x * kSlot;
   if (NW > 1 && threadIdx.x >= 32) {
     tile_helper_loop<NT, NW>(P, pl, smem, Hg);
@@ -359,7 +359,7 @@ static lmpc_status launch_tile_nw(lmpc_handle* h, const KBatch& kb, cudaStream_t
   if (occ < 1) { set_err("tile solve kernel does not fit on an SM"); return LMPC_ERR_CUDA; }
   int grid = h->num_sms * occ;
   if (grid > kb.B) grid = kb.B;
-  const size_t slot = (size_t)lmpc::TileGeom<NT>::HS + 6 * lmpc::TileGeom<NT>::NBMAX + 2;
+  const size_t slot = lmpc::tile_slot_doubles<NT>();
   CK(wsbuf->ensure((size_t)grid * slot * sizeof(double)));
   KBatch k = kb;
   k.order = order;
@@ -373,6 +373,7 @@ template <int NT>
 static lmpc_status launch_tile(lmpc_handle* h, const KBatch& kb, cudaStream_t s, DevBuf* wsbuf, int* order, int* count,
                                int* work) {
   int nw = NT == lmpc::kTileA ? kTileWarpsA : kTileWarpsB;
+  if (NT > lmpc::kTileB) return launch_tile_nw<NT, 4>(h, kb, s, wsbuf, order, count, work);
   if (kb.B <= h->num_sms) nw = 4;  // fewer problems than SMs: latency counts, occupancy does not
   if (const char* e = getenv("LMPC_TILE_NW")) nw = atoi(e);
   if (nw == 1) return launch_tile_nw<NT, 1>(h, kb, s, wsbuf, order, count, work);
@@ -397,7 +398,9 @@ static lmpc_status launch_solve(lmpc_handle* h, KBatch kb, cudaStream_t s) {
   CK(cudaEventRecord(h->ev0, s));
   lmpc::classify_kernel<<<(kb.B + 255) / 256, 256, 0, s>>>(kb.contact, H, kb.B, dstats, order, stride, ctr + 4);
   h->launches++;
-  const bool may3 = 12 * H > 8 * lmpc::kTileB;
+  const bool big = 12 * H > 8 * lmpc::kTileB;
+  static const bool cls3_cta = getenv("LMPC_CLS3") && !strcmp(getenv("LMPC_CLS3"), "cta");  // the scalar CTA kernel, kept for comparison
+  const bool may3 = big && cls3_cta;
   if (may3) {
     CK(cudaMemcpyAsync(h->h_cls, &dstats->n_max, sizeof(int), cudaMemcpyDeviceToHost, s));
     CK(cudaMemcpyAsync(h->h_cls + 1, ctr + 7, sizeof(int), cudaMemcpyDeviceToHost, s));
@@ -427,6 +430,10 @@ static lmpc_status launch_solve(lmpc_handle* h, KBatch kb, cudaStream_t s) {
   }
   if (12 * H > 8 * lmpc::kTileA) {
     lmpc_status st = launch_tile<lmpc::kTileB>(h, kb, s, &h->d_wsT2, order + 2 * (size_t)stride, ctr + 6, ctr + 2);
+    if (st != LMPC_OK) return st;
+  }
+  if (big && !cls3_cta) {  // class 3 (n > 192): 48 x 48 tiles, 4 warps per QP, factor in the global workspace slot
+    lmpc_status st = launch_tile<lmpc::kTileC>(h, kb, s, &h->d_ws, order + 3 * (size_t)stride, ctr + 7, ctr + 3);
     if (st != LMPC_OK) return st;
   }
   if (may3) {

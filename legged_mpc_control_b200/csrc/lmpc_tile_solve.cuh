@@ -16,6 +16,20 @@ struct TilePlan {
   int n_doubles;
   int oBLK, oFACE, oBMAP, total_bytes;
 };
+// NT above this keeps the factor in the CTA's global (L2 / HBM) workspace slot instead of shared memory.
+constexpr int kTileSmemMaxNT = 24;
+template <int NT>
+__host__ __device__ inline size_t tile_slot_doubles() {
+  using G = TileGeom<NT>;
+  return (size_t)G::HS + 6 * G::NBMAX + 2 + (NT > kTileSmemMaxNT ? (size_t)G::LS : 0);
+}
+// factor storage of this CTA
+template <int NT>
+__device__ __forceinline__ double* tile_ls(const TilePlan& pl, unsigned char* smem, double* Hg) {
+  using G = TileGeom<NT>;
+  if (NT > kTileSmemMaxNT) return Hg + G::HS + 6 * G::NBMAX + 2;
+  return reinterpret_cast<double*>(smem) + pl.oLS;
+}
 template <int NT>
 __host__ __device__ inline TilePlan make_tile_plan(int H) {
   using G = TileGeom<NT>;
@@ -25,7 +39,7 @@ __host__ __device__ inline TilePlan make_tile_plan(int H) {
   p.oBW = s; s += 36;
   p.oCOS = s; s += H; p.oSIN = s; s += H; p.oCS = s; s += H; p.oSS = s; s += H;
   p.oE = s; s += 12 * H; p.oAJ = s; s += 3 * H; p.oBJ = s; s += 3 * H;
-  int o = s > G::LS ? s : G::LS;
+  int o = (NT > kTileSmemMaxNT || s > G::LS) ? s : G::LS;  // the setup scratch aliases the factor when that lives here
   p.oU = o; o += G::N;
   p.oGS = o; o += G::N;
   p.oHU = o; o += G::N;
@@ -122,7 +136,7 @@ __device__ void tile_reduced_matrix(const TilePlan& pl, unsigned char* smem, con
                                     int tid, int nthr) {
   using G = TileGeom<NT>;
   constexpr int N = G::N;
-  double* Ls = reinterpret_cast<double*>(smem) + pl.oLS;
+  double* Ls = tile_ls<NT>(pl, smem, const_cast<double*>(Hg));
   const signed char* face = reinterpret_cast<const signed char*>(smem + pl.oFACE);
   const int npairs = (nb * (nb + 1)) >> 1;
   for (int pr = tid; pr < npairs; pr += nthr) {
@@ -209,8 +223,8 @@ __device__ __forceinline__ void tile_helper_loop(const KParams& P, const TilePla
     __syncthreads();
     const int job = *tile_job();
     if (job == 0) return;
-    if (job == 1) gm_factor_mw<NT, true, NW>(Hg, sd + pl.oLS, sd + pl.oXB, w);
-    else if (job == 2) gm_factor_mw<NT, false, NW>(Hg, sd + pl.oLS, sd + pl.oXB, w);
+    if (job == 1) gm_factor_mw<NT, true, NW>(Hg, tile_ls<NT>(pl, smem, Hg), sd + pl.oXB, w);
+    else if (job == 2) gm_factor_mw<NT, false, NW>(Hg, tile_ls<NT>(pl, smem, Hg), sd + pl.oXB, w);
     else {
       const TileJobArgs a = *tile_job_args();
       if (job == 3) tile_hessian_blocks<NT>(P, pl, smem, Hg, a.nb, a.n, a.sc, a.im2, threadIdx.x, 32 * NW);
@@ -229,7 +243,7 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
   const int lane = threadIdx.x & 31;
   const int H = P.H;
   double* sd = reinterpret_cast<double*>(smem);
-  double* Ls = sd + pl.oLS;
+  double* Ls = tile_ls<NT>(pl, smem, Hg);
   double* u = sd + pl.oU;
   double* gs = sd + pl.oGS;
   double* hu = sd + pl.oHU;
