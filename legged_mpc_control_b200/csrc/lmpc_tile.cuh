@@ -29,9 +29,10 @@ struct TileGeom {
 // One tile column of the factorization with a compile-time tile count CNT = NT - J (static
 // accumulator indices, no predicated tensor instructions); the K loop stays rolled.
 template <int NT, int CNT, bool FROM_G>
-__device__ __forceinline__ bool gm_column(const double2* Mf, double2* Lf, double* xb) {
+__device__ __forceinline__ bool gm_column(const double2* Mf, double2* Lf, double* xb, int nte) {
   using G = TileGeom<NT>;
   constexpr int J = NT - CNT;
+  if (J >= nte) return false;  // identity padding beyond the problem's own tile count: never read back
   double2* colL = Lf + 32 * G::lcol(J);              // tile (J + i, J) at colL[32 i]
   const double2* colM = Mf + 32 * (J * NT + J);      // tile (J + i, J) at colM[32 NT i]
   double2 acc[CNT];
@@ -64,25 +65,25 @@ __device__ __forceinline__ bool gm_column(const double2* Mf, double2* Lf, double
 }
 template <int NT, int CNT, bool FROM_G>
 struct GmColumns {
-  __device__ static __forceinline__ bool run(const double2* Mf, double2* Lf, double* xb) {
-    const bool b = gm_column<NT, CNT, FROM_G>(Mf, Lf, xb);
-    return GmColumns<NT, CNT - 1, FROM_G>::run(Mf, Lf, xb) || b;
+  __device__ static __forceinline__ bool run(const double2* Mf, double2* Lf, double* xb, int nte) {
+    const bool b = gm_column<NT, CNT, FROM_G>(Mf, Lf, xb, nte);
+    return GmColumns<NT, CNT - 1, FROM_G>::run(Mf, Lf, xb, nte) || b;
   }
 };
 template <int NT, bool FROM_G>
 struct GmColumns<NT, 0, FROM_G> {
-  __device__ static __forceinline__ bool run(const double2*, double2*, double*) { return false; }
+  __device__ static __forceinline__ bool run(const double2*, double2*, double*, int) { return false; }
 };
 
 // Factor M = L L' on NT x NT tiles.  FROM_G: lower tiles of M read from the workspace Mg (L2);
 // !FROM_G: M's lower tiles are already in Ls (diagonal tiles full symmetric).  On exit Ls holds
 // L_IJ (I > J) and inv(L_JJ) in the diagonal slots.  Returns false on a non-positive pivot.
 template <int NT, bool FROM_G>
-__device__ __noinline__ bool gm_factor(const double* Mg, double* Ls, double* xb) {
+__device__ __noinline__ bool gm_factor(const double* Mg, double* Ls, double* xb, int nte) {
   const int lane = threadIdx.x & 31;
   double2* Lf = reinterpret_cast<double2*>(Ls) + lane;
   const double2* Mf = reinterpret_cast<const double2*>(Mg) + lane;
-  const bool bad = GmColumns<NT, NT, FROM_G>::run(Mf, Lf, xb);
+  const bool bad = GmColumns<NT, NT, FROM_G>::run(Mf, Lf, xb, nte);
   const bool ok = !__any_sync(0xffffffffu, bad);
   __syncwarp();
   return ok;
@@ -94,9 +95,10 @@ __device__ __noinline__ bool gm_factor(const double* Mg, double* Ls, double* xb)
 // that accumulator indices stay static; a helper warp whose share of a late column is empty only
 // passes the barriers.  Everything else of the solve stays on warp 0.
 template <int NT, int CNT, bool FROM_G, int NW, int W>
-__device__ __forceinline__ bool gm_column_mw(const double2* Mf, double2* Lf, double* xb) {
+__device__ __forceinline__ bool gm_column_mw(const double2* Mf, double2* Lf, double* xb, int nte) {
   using G = TileGeom<NT>;
   constexpr int J = NT - CNT;
+  if (J >= nte) return false;  // CTA-uniform: every warp skips the padded columns and their barriers
   constexpr int CW = CNT > W ? (CNT - W + NW - 1) / NW : 0;  // tiles of this column owned by warp W
   double2* colL = Lf + 32 * G::lcol(J);
   const double2* colM = Mf + 32 * (J * NT + J);
@@ -139,30 +141,30 @@ __device__ __forceinline__ bool gm_column_mw(const double2* Mf, double2* Lf, dou
 }
 template <int NT, int CNT, bool FROM_G, int NW, int W>
 struct GmColumnsMW {
-  __device__ static __forceinline__ bool run(const double2* Mf, double2* Lf, double* xb) {
-    const bool b = gm_column_mw<NT, CNT, FROM_G, NW, W>(Mf, Lf, xb);
-    return GmColumnsMW<NT, CNT - 1, FROM_G, NW, W>::run(Mf, Lf, xb) || b;
+  __device__ static __forceinline__ bool run(const double2* Mf, double2* Lf, double* xb, int nte) {
+    const bool b = gm_column_mw<NT, CNT, FROM_G, NW, W>(Mf, Lf, xb, nte);
+    return GmColumnsMW<NT, CNT - 1, FROM_G, NW, W>::run(Mf, Lf, xb, nte) || b;
   }
 };
 template <int NT, bool FROM_G, int NW, int W>
 struct GmColumnsMW<NT, 0, FROM_G, NW, W> {
-  __device__ static __forceinline__ bool run(const double2*, double2*, double*) { return false; }
+  __device__ static __forceinline__ bool run(const double2*, double2*, double*, int) { return false; }
 };
 template <int NT, bool FROM_G, int NW, int W>
-__device__ __noinline__ bool gm_factor_mw_w(const double* Mg, double* Ls, double* xb) {
+__device__ __noinline__ bool gm_factor_mw_w(const double* Mg, double* Ls, double* xb, int nte) {
   const int lane = threadIdx.x & 31;
   double2* Lf = reinterpret_cast<double2*>(Ls) + lane;
   const double2* Mf = reinterpret_cast<const double2*>(Mg) + lane;
-  const bool bad = GmColumnsMW<NT, NT, FROM_G, NW, W>::run(Mf, Lf, xb);
+  const bool bad = GmColumnsMW<NT, NT, FROM_G, NW, W>::run(Mf, Lf, xb, nte);
   return !__any_sync(0xffffffffu, bad);
 }
 // Entry for warp `w` of the CTA (every warp of the CTA must call it; only warp 0's result counts).
 template <int NT, bool FROM_G, int NW>
-__device__ __forceinline__ bool gm_factor_mw(const double* Mg, double* Ls, double* xb, int w) {
-  if (NW >= 2 && w == 1) return gm_factor_mw_w<NT, FROM_G, NW, (NW >= 2 ? 1 : 0)>(Mg, Ls, xb);
-  if (NW >= 4 && w == 2) return gm_factor_mw_w<NT, FROM_G, NW, (NW >= 4 ? 2 : 0)>(Mg, Ls, xb);
-  if (NW >= 4 && w == 3) return gm_factor_mw_w<NT, FROM_G, NW, (NW >= 4 ? 3 : 0)>(Mg, Ls, xb);
-  return gm_factor_mw_w<NT, FROM_G, NW, 0>(Mg, Ls, xb);
+__device__ __forceinline__ bool gm_factor_mw(const double* Mg, double* Ls, double* xb, int w, int nte) {
+  if (NW >= 2 && w == 1) return gm_factor_mw_w<NT, FROM_G, NW, (NW >= 2 ? 1 : 0)>(Mg, Ls, xb, nte);
+  if (NW >= 4 && w == 2) return gm_factor_mw_w<NT, FROM_G, NW, (NW >= 4 ? 2 : 0)>(Mg, Ls, xb, nte);
+  if (NW >= 4 && w == 3) return gm_factor_mw_w<NT, FROM_G, NW, (NW >= 4 ? 3 : 0)>(Mg, Ls, xb, nte);
+  return gm_factor_mw_w<NT, FROM_G, NW, 0>(Mg, Ls, xb, nte);
 }
 // Job mailbox of the CTA: 0 exit, 1 factor from the L2 workspace, 2 factor in place, 3 Hessian
 // blocks, 4 reduced matrix of the polish (lmpc_tile_solve.cuh).
@@ -171,12 +173,16 @@ __device__ __forceinline__ int* tile_job() {
   return &job;
 }
 // What warp 0 calls in place of gm_factor.
+__device__ __forceinline__ int* tile_job_nte() {
+  __shared__ int nte;
+  return &nte;
+}
 template <int NT, int NW, bool FROM_G>
-__device__ __forceinline__ bool tile_factor(const double* Mg, double* Ls, double* xb) {
-  if (NW == 1) return gm_factor<NT, FROM_G>(Mg, Ls, xb);
-  if ((threadIdx.x & 31) == 0) *tile_job() = FROM_G ? 1 : 2;
+__device__ __forceinline__ bool tile_factor(const double* Mg, double* Ls, double* xb, int nte) {
+  if (NW == 1) return gm_factor<NT, FROM_G>(Mg, Ls, xb, nte);
+  if ((threadIdx.x & 31) == 0) { *tile_job_nte() = nte; *tile_job() = FROM_G ? 1 : 2; }
   __syncthreads();  // releases the helper warps; also publishes warp 0's writes of M
-  const bool ok = gm_factor_mw<NT, FROM_G, NW>(Mg, Ls, xb, 0);
+  const bool ok = gm_factor_mw<NT, FROM_G, NW>(Mg, Ls, xb, 0, nte);
   __syncwarp();
   return ok;
 }
@@ -184,14 +190,14 @@ __device__ __forceinline__ bool tile_factor(const double* Mg, double* Ls, double
 // substitution in t-layout; the solved blocks are read back from x itself (every lane re-reads the
 // pair it wrote, so no barrier is needed inside).  Caller syncs before and after.
 template <int NT>
-__device__ __noinline__ void gm_solve(const double* Ls, double* x) {
+__device__ __forceinline__ void gm_solve_impl(const double* Ls, double* x, const int nte) {
   using G = TileGeom<NT>;
   const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   const double2* Lf = reinterpret_cast<const double2*>(Ls) + lane;
   double2* xt = reinterpret_cast<double2*>(x) + t;  // block K pair at xt[4 K]
   // forward: y_J = inv(L_JJ) (b_J - sum_{K<J} L_JK y_K)
 #pragma unroll 1
-  for (int J = 0; J < NT; ++J) {
+  for (int J = 0; J < nte; ++J) {  // blocks beyond the problem's own tile count are identity with zero right-hand sides
     double p0 = 0.0, p1 = 0.0;
     const double2* p = Lf + 32 * J;  // tile (J, 0); tile (J, K+1) is NT - K - 1 tiles further
 #pragma unroll 4
@@ -212,38 +218,44 @@ __device__ __noinline__ void gm_solve(const double* Ls, double* x) {
   }
   // backward: x_J = inv(L_JJ)' (y_J - sum_{I>J} L_IJ' x_I)
 #pragma unroll 1
-  for (int J = NT - 1; J >= 0; --J) {
+  for (int J = nte - 1; J >= 0; --J) {
     const double* ct = Ls + 64 * G::lcol(J) + 16 * t + g;  // transposed reads of column J: tile i at ct[64 i], ct[64 i + 8]
     double p0 = 0.0, p1 = 0.0;
 #pragma unroll 4
-    for (int i = 1; i < NT - J; ++i) {
+    for (int i = 1; i < nte - J; ++i) {
       const double2 xi = xt[4 * (J + i)];
       p0 = fma(ct[64 * i], xi.x, p0);
       p1 = fma(ct[64 * i + 8], xi.y, p1);
     }
     double2 r = xt[4 * J];
-    if (J < NT - 1) {
+    if (J < nte - 1) {
       const double2 s = quad_reduce_t(p0 + p1);
       r.x -= s.x; r.y -= s.y;
     }
     xt[4 * J] = quad_reduce_t(fma(ct[0], r.x, ct[8] * r.y));
   }
 }
+// nte = tiles this problem fills (<= NT).  The full-size case keeps its compile-time trip counts.
+template <int NT>
+__device__ __noinline__ void gm_solve(const double* Ls, double* x, int nte) {
+  if (nte == NT) gm_solve_impl<NT>(Ls, x, NT);
+  else gm_solve_impl<NT>(Ls, x, nte);
+}
 
 // y = H x for the full-symmetric workspace (global, L2); x, y (8 NT)-vectors in shared memory.
 // Tile rows I = i0, i0 + di, ...: one warp does them all (i0 = 0, di = 1) or the warps of the CTA
 // take every NW-th row (job 5).
 template <int NT>
-__device__ __noinline__ void gm_symv(const double* Hg, const double* x, double* y, int i0 = 0, int di = 1) {
+__device__ __forceinline__ void gm_symv_impl(const double* Hg, const double* x, double* y, const int nte, int i0, int di) {
   const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   const double2* Hf = reinterpret_cast<const double2*>(Hg) + lane;
   const double2* xt = reinterpret_cast<const double2*>(x) + t;
 #pragma unroll 1
-  for (int I = i0; I < NT; I += di) {
+  for (int I = i0; I < nte; I += di) {  // rows / columns beyond nte are identity padding times zeros: y stays 0 there
     double p0 = 0.0, p1 = 0.0;
     const double2* row = Hf + 32 * (I * NT);
 #pragma unroll 8
-    for (int J = 0; J < NT; ++J) {
+    for (int J = 0; J < nte; ++J) {
       const double2 h = __ldcg(row + 32 * J);
       const double2 v = xt[4 * J];
       p0 = fma(h.x, v.x, p0);
@@ -252,6 +264,11 @@ __device__ __noinline__ void gm_symv(const double* Hg, const double* x, double* 
     const double2 s = quad_reduce_t(p0 + p1);
     if (g == 0) *reinterpret_cast<double2*>(y + 8 * I + 2 * t) = s;
   }
+}
+template <int NT>
+__device__ __noinline__ void gm_symv(const double* Hg, const double* x, double* y, int nte, int i0 = 0, int di = 1) {
+  if (nte == NT) gm_symv_impl<NT>(Hg, x, y, NT, i0, di);
+  else gm_symv_impl<NT>(Hg, x, y, nte, i0, di);
 }
 
 }  // namespace lmpc

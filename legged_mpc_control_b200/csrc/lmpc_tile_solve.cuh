@@ -177,7 +177,7 @@ __device__ void tile_reduced_matrix(const TilePlan& pl, unsigned char* smem, con
 }
 
 // Mailbox arguments of the shared jobs.
-struct TileJobArgs { int nb, n; double sc, im2, mu; const double* x; double* y; };
+struct TileJobArgs { int nb, n, nte; double sc, im2, mu; const double* x; double* y; };
 __device__ __forceinline__ TileJobArgs* tile_job_args() {
   __shared__ TileJobArgs a;
   return &a;
@@ -203,15 +203,15 @@ __device__ __forceinline__ void tile_shared(int job, const KParams& P, const Til
 }
 // y = H x with the tile rows dealt over the warps of the CTA (job 5); x, y in shared memory.
 template <int NT, int NW>
-__device__ __forceinline__ void tile_symv(const double* Hg, const double* x, double* y) {
-  if (NW == 1) { gm_symv<NT>(Hg, x, y); return; }
+__device__ __forceinline__ void tile_symv(const double* Hg, const double* x, double* y, int nte) {
+  if (NW == 1) { gm_symv<NT>(Hg, x, y, nte); return; }
   if ((threadIdx.x & 31) == 0) {
     TileJobArgs* a = tile_job_args();
-    a->x = x; a->y = y;
+    a->x = x; a->y = y; a->nte = nte;
     *tile_job() = 5;
   }
   __syncthreads();
-  gm_symv<NT>(Hg, x, y, 0, NW);
+  gm_symv<NT>(Hg, x, y, nte, 0, NW);
   __syncthreads();
 }
 // Helper warps (1 .. NW-1) live here until warp 0 posts job 0.
@@ -223,13 +223,13 @@ __device__ __forceinline__ void tile_helper_loop(const KParams& P, const TilePla
     __syncthreads();
     const int job = *tile_job();
     if (job == 0) return;
-    if (job == 1) gm_factor_mw<NT, true, NW>(Hg, tile_ls<NT>(pl, smem, Hg), sd + pl.oXB, w);
-    else if (job == 2) gm_factor_mw<NT, false, NW>(Hg, tile_ls<NT>(pl, smem, Hg), sd + pl.oXB, w);
+    if (job == 1) gm_factor_mw<NT, true, NW>(Hg, tile_ls<NT>(pl, smem, Hg), sd + pl.oXB, w, *tile_job_nte());
+    else if (job == 2) gm_factor_mw<NT, false, NW>(Hg, tile_ls<NT>(pl, smem, Hg), sd + pl.oXB, w, *tile_job_nte());
     else {
       const TileJobArgs a = *tile_job_args();
       if (job == 3) tile_hessian_blocks<NT>(P, pl, smem, Hg, a.nb, a.n, a.sc, a.im2, threadIdx.x, 32 * NW);
       else if (job == 4) tile_reduced_matrix<NT>(pl, smem, Hg, a.nb, a.n, a.mu, threadIdx.x, 32 * NW);
-      else gm_symv<NT>(Hg, a.x, a.y, w, NW);
+      else gm_symv<NT>(Hg, a.x, a.y, a.nte, w, NW);
       __syncthreads();
     }
   }
@@ -332,6 +332,7 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
   }
   __syncwarp();
   const int n = 3 * nb;
+  const int nte = max(1, (n + 7) >> 3);  // 8x8 tiles this problem fills; the rest of NT is identity padding
   const double mu = prm[PRM_MU], fzm = prm[PRM_FZ], mass = prm[PRM_MASS];
   const double* qw = prm + PRM_Q;
   const double* rw = prm + PRM_R;
@@ -462,7 +463,7 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
     if (stage >= 0 && !ipm_inited) {  // interior-point start (skipped entirely by a verified warm start)
       ipm_inited = true;
       {
-        tile_symv<NT, NW>(Hg, u, hu);
+        tile_symv<NT, NW>(Hg, u, hu, nte);
         __syncwarp();
         double gi = 0, ssum = 0;
         for (int i = lane; i < N; i += 32) gi = fmax(gi, fabs(hu[i] + gs[i]));
@@ -513,7 +514,7 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
           blk_store<NT>(Hg, b, hd);
         }
         __syncwarp();
-        tile_symv<NT, NW>(Hg, u, hu);
+        tile_symv<NT, NW>(Hg, u, hu, nte);
         __syncwarp();
         double ri = 0;
         for (int b = lane; b < nb; b += 32) {
@@ -549,8 +550,8 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
         for (int a = 0; a < 3; ++a) dua[3 * b + a] = -(hu[3 * b + a] + gs[3 * b + a]);
       }
       __syncwarp();
-      if (!tile_factor<NT, NW, true>(Hg, Ls, xb)) { ipm_broken = true; break; }
-      gm_solve<NT>(Ls, dua);
+      if (!tile_factor<NT, NW, true>(Hg, Ls, xb, nte)) { ipm_broken = true; break; }
+      gm_solve<NT>(Ls, dua, nte);
       __syncwarp();
       double tau = 0.0;
       for (int b = lane; b < nb; b += 32) {
@@ -595,7 +596,7 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
         }
       }
       __syncwarp();
-      gm_solve<NT>(Ls, du);
+      gm_solve<NT>(Ls, du, nte);
       __syncwarp();
       double tau2 = 0.0;
       for (int b = lane; b < nb; b += 32) {
@@ -688,7 +689,7 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
       }
       __syncwarp();
       if (__any_sync(0xffffffffu, pinned_top)) {
-        tile_symv<NT, NW>(Hg, rd, hu);
+        tile_symv<NT, NW>(Hg, rd, hu, nte);
       } else {  // p = 0: H p = 0 without reading H
         for (int i = lane; i < N; i += 32) hu[i] = 0.0;
       }
@@ -707,8 +708,8 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
         du[3 * b + 2] = (apex || top) ? 0.0 : -gzt;
       }
       __syncwarp();
-      if (!tile_factor<NT, NW, false>(Hg, Ls, xb)) break;
-      gm_solve<NT>(Ls, du);
+      if (!tile_factor<NT, NW, false>(Hg, Ls, xb, nte)) break;
+      gm_solve<NT>(Ls, du, nte);
       for (int i = lane; i < N; i += 32) dua[i] = 0.0;
       __syncwarp();
       for (int b = lane; b < nb; b += 32) {
@@ -719,7 +720,7 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
         dua[3 * b + 2] = vz + rd[3 * b + 2];
       }
       __syncwarp();
-      tile_symv<NT, NW>(Hg, dua, hu);
+      tile_symv<NT, NW>(Hg, dua, hu, nte);
       __syncwarp();
       int changed = 0;
       for (int b = lane; b < nb; b += 32) {
@@ -768,7 +769,7 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
       break;
     } else {
       // back to the interior point at a tighter mu: H u of the interior iterate is needed again
-      tile_symv<NT, NW>(Hg, u, hu);
+      tile_symv<NT, NW>(Hg, u, hu, nte);
       __syncwarp();
     }
   }
