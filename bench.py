@@ -305,7 +305,7 @@ def run_b200(args):
             "roofline": {
                 "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
                 "traffic": _ncu_traffic() if _WL == "headline" else None,
-                "traffic_source": "profiles/r01_v14_ncu_full_solve_warp_kernel.csv (bytes per launch; input reads + write-backs of the L2-resident "
+                "traffic_source": "profiles/r01_v15_ncu_full_solve_warp_kernel.csv (bytes per launch; input reads + write-backs of the L2-resident "
                                   "Hessian workspace, <0.1% of HBM peak: the bound is FP64 latency, not DRAM)",
                 "kernel": "lmpc::solve_warp_kernel" if stats["mean_n_eff"] <= 63 else "lmpc::solve_tile_kernel / solve_kernel (by size class)",
                 "kernel_ms": kms,
@@ -424,7 +424,7 @@ def run_c1(args):
 def _ncu_traffic():
     """dram__bytes_read.sum + dram__bytes_write.sum of one solve_warp_kernel launch of the headline
     workload, from the committed `ncu --set full` capture (bench.py never runs under a profiler)."""
-    path = os.path.join(ROOT, "profiles", "r01_v14_ncu_full_solve_warp_kernel.csv")
+    path = os.path.join(ROOT, "profiles", "r01_v15_ncu_full_solve_warp_kernel.csv")
     try:
         tot = 0.0
         for ln in open(path):
