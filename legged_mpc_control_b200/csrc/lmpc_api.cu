@@ -22,7 +22,8 @@ namespace lmpc {
 //   0: n <= 63            one warp per QP, 8 x 8 tiles        (solve_warp_kernel)
 //   1: 64 <= n <= 120     one warp per QP, 15 x 15 tiles      (solve_tile_kernel<15>)
 //   2: 121 <= n <= 192    one warp per QP, 24 x 24 tiles      (solve_tile_kernel<24>)
-//   3: n > 192            one CTA per QP, packed matrices     (solve_kernel)
+//   4: 193 <= n <= 288    4 warps per QP, 36 x 36 tiles       (solve_tile_kernel<36>), factor in the global slot
+//   3: n > 288            4 warps per QP, 48 x 48 tiles       (solve_tile_kernel<48>); LMPC_CLS3=cta: scalar CTA kernel (solve_kernel)
 // Register cap of the one-warp kernel, measured on B200 (headline workload, solves/s):
 //   __launch_bounds__(32, 9): ptxas settles on 168 registers, 600 B of spills, 9 warps/SM   3.75 M
 //   __maxnreg__(224):         290 B of spills, 9 warps/SM                                   3.90 M
@@ -31,10 +32,12 @@ namespace lmpc {
 #ifndef LMPC_WARP_MAXNREG
 #define LMPC_WARP_MAXNREG 255
 #endif
-constexpr int kNumClasses = 4;
+constexpr int kNumClasses = 5;
+constexpr int kCtrCount = 8;  // counter block: work counters at [c], class sizes at [kCtrCount + c]
 constexpr int kTileA = 15, kTileB = 24, kTileC = 48;  // 8 x 48 = 384 = 12 x LMPC_MAX_HORIZON
+constexpr int kTileD = 36;  // class 4: 192 < n <= 288 (crawl at H = 30, stand at H = 20), same kernel as class 3
 __host__ __device__ inline int size_class(int n) {
-  return n <= 3 * WNBMAX ? 0 : (n <= 8 * kTileA ? 1 : (n <= 8 * kTileB ? 2 : 3));
+  return n <= 3 * WNBMAX ? 0 : (n <= 8 * kTileA ? 1 : (n <= 8 * kTileB ? 2 : (n <= 8 * kTileD ? 4 : 3)));
 }
 
 // Compacts the problems of every size class into its own index list (order + cls * B) with
@@ -220,7 +223,7 @@ struct lmpc_handle {
   // device staging for host-pointer calls
   DevBuf d_x0, d_rot, d_foot, d_cmd, d_contact, d_q, d_r, d_mu, d_fz, d_mass, d_inertia;
   DevBuf d_grf, d_status, d_iters, d_active, d_U;
-  DevBuf d_stats, d_counter, d_ws, d_wsA, d_wsT1, d_wsT2, d_order, d_warm;
+  DevBuf d_stats, d_counter, d_ws, d_wsA, d_wsT1, d_wsT2, d_wsT3, d_order, d_warm;
   bool warm_enabled = false;
   int warm_shift = 1;
   // small-batch host path: one packed H2D and one packed D2H (a single robot's tick is latency-bound)
@@ -316,8 +319,8 @@ extern "C" lmpc_status lmpc_create(const lmpc_params* params, int32_t max_batch,
   CK(cudaEventCreateWithFlags(&h->ev_cls, cudaEventDisableTiming));
   CK(cudaMallocHost((void**)&h->h_cls, 4 * sizeof(int)));
   CK(h->d_stats.ensure(sizeof(KStats)));
-  CK(h->d_counter.ensure(8 * sizeof(int)));  // work counters [4], class sizes [4]
-  CK(h->d_order.ensure(4 * (size_t)max_batch * sizeof(int)));
+  CK(h->d_counter.ensure(2 * lmpc::kCtrCount * sizeof(int)));  // work counters, class sizes
+  CK(h->d_order.ensure(lmpc::kNumClasses * (size_t)max_batch * sizeof(int)));
   memset(&h->last_stats, 0, sizeof(KStats));
   *out = h;
   if (params->solver == LMPC_SOLVER_ACTIVE_SET) {  // the face records are this solver's state
@@ -333,7 +336,7 @@ extern "C" void lmpc_destroy(lmpc_handle* h) {
   if (h->stream) cudaStreamSynchronize(h->stream);
   DevBuf* bufs[] = {&h->d_x0, &h->d_rot, &h->d_foot, &h->d_cmd, &h->d_contact, &h->d_q, &h->d_r, &h->d_mu,
                     &h->d_fz, &h->d_mass, &h->d_inertia, &h->d_grf, &h->d_status, &h->d_iters, &h->d_active,
-                    &h->d_U, &h->d_stats, &h->d_counter, &h->d_ws, &h->d_wsA, &h->d_wsT1, &h->d_wsT2, &h->d_order, &h->d_warm,
+                    &h->d_U, &h->d_stats, &h->d_counter, &h->d_ws, &h->d_wsA, &h->d_wsT1, &h->d_wsT2, &h->d_wsT3, &h->d_order, &h->d_warm,
                     &h->d_pin, &h->d_pout, &h->d_rx, &h->d_rfw, &h->d_rph, &h->d_rgait, &h->d_rspeed, &h->d_rtot, &h->d_xlog, &h->d_glog};
   for (DevBuf* b : bufs) b->release();
   if (h->ev0) cudaEventDestroy(h->ev0);
@@ -390,20 +393,21 @@ static lmpc_status launch_solve(lmpc_handle* h, KBatch kb, cudaStream_t s) {
   kb.warm = h->warm_enabled ? (uint8_t*)h->d_warm.p : nullptr;
   kb.warm_shift = h->warm_shift;
   KStats* dstats = (KStats*)h->d_stats.p;
-  int* ctr = (int*)h->d_counter.p;  // [0..3] work counters, [4..7] class sizes
+  int* ctr = (int*)h->d_counter.p;  // [c] work counters, [kCtrCount + c] class sizes
+  int* cnt = ctr + lmpc::kCtrCount;
   int* order = (int*)h->d_order.p;  // class c at order + c * max_batch
   const int stride = h->max_batch;
   CK(cudaMemsetAsync(dstats, 0, sizeof(KStats), s));
-  CK(cudaMemsetAsync(ctr, 0, 8 * sizeof(int), s));
+  CK(cudaMemsetAsync(ctr, 0, 2 * lmpc::kCtrCount * sizeof(int), s));
   CK(cudaEventRecord(h->ev0, s));
-  lmpc::classify_kernel<<<(kb.B + 255) / 256, 256, 0, s>>>(kb.contact, H, kb.B, dstats, order, stride, ctr + 4);
+  lmpc::classify_kernel<<<(kb.B + 255) / 256, 256, 0, s>>>(kb.contact, H, kb.B, dstats, order, stride, cnt);
   h->launches++;
   const bool big = 12 * H > 8 * lmpc::kTileB;
   static const bool cls3_cta = getenv("LMPC_CLS3") && !strcmp(getenv("LMPC_CLS3"), "cta");  // the scalar CTA kernel, kept for comparison
   const bool may3 = big && cls3_cta;
   if (may3) {
     CK(cudaMemcpyAsync(h->h_cls, &dstats->n_max, sizeof(int), cudaMemcpyDeviceToHost, s));
-    CK(cudaMemcpyAsync(h->h_cls + 1, ctr + 7, sizeof(int), cudaMemcpyDeviceToHost, s));
+    CK(cudaMemcpyAsync(h->h_cls + 1, cnt + 3, sizeof(int), cudaMemcpyDeviceToHost, s));
     CK(cudaEventRecord(h->ev_cls, s));
   }
   // ---- class 0: one warp per QP, 8 x 8 tiles
@@ -419,21 +423,25 @@ static lmpc_status launch_solve(lmpc_handle* h, KBatch kb, cudaStream_t s) {
     CK(h->d_wsA.ensure((size_t)grid * lmpc::WN * lmpc::WN * sizeof(double)));
     KBatch ka = kb;
     ka.order = order;
-    kernA<<<grid, 32, wp.total_bytes, s>>>(h->kp, ka, dstats, (double*)h->d_wsA.p, ctr + 4, ctr + 0);
+    kernA<<<grid, 32, wp.total_bytes, s>>>(h->kp, ka, dstats, (double*)h->d_wsA.p, cnt + 0, ctr + 0);
     h->launches++;
     CK(cudaGetLastError());
   }
   // ---- classes 1, 2: one warp per QP, 15 x 15 / 24 x 24 tiles (only if the horizon can reach them)
   if (12 * H > 3 * lmpc::WNBMAX) {
-    lmpc_status st = launch_tile<lmpc::kTileA>(h, kb, s, &h->d_wsT1, order + stride, ctr + 5, ctr + 1);
+    lmpc_status st = launch_tile<lmpc::kTileA>(h, kb, s, &h->d_wsT1, order + stride, cnt + 1, ctr + 1);
     if (st != LMPC_OK) return st;
   }
   if (12 * H > 8 * lmpc::kTileA) {
-    lmpc_status st = launch_tile<lmpc::kTileB>(h, kb, s, &h->d_wsT2, order + 2 * (size_t)stride, ctr + 6, ctr + 2);
+    lmpc_status st = launch_tile<lmpc::kTileB>(h, kb, s, &h->d_wsT2, order + 2 * (size_t)stride, cnt + 2, ctr + 2);
     if (st != LMPC_OK) return st;
   }
   if (big && !cls3_cta) {  // class 3 (n > 192): 48 x 48 tiles, 4 warps per QP, factor in the global workspace slot
-    lmpc_status st = launch_tile<lmpc::kTileC>(h, kb, s, &h->d_ws, order + 3 * (size_t)stride, ctr + 7, ctr + 3);
+    lmpc_status st = launch_tile<lmpc::kTileC>(h, kb, s, &h->d_ws, order + 3 * (size_t)stride, cnt + 3, ctr + 3);
+    if (st != LMPC_OK) return st;
+  }
+  if (big) {  // class 4 (192 < n <= 288): 36 x 36 tiles, otherwise as class 3
+    lmpc_status st = launch_tile<lmpc::kTileD>(h, kb, s, &h->d_wsT3, order + 4 * (size_t)stride, cnt + 4, ctr + 4);
     if (st != LMPC_OK) return st;
   }
   if (may3) {
@@ -467,7 +475,7 @@ static lmpc_status launch_solve(lmpc_handle* h, KBatch kb, cudaStream_t s) {
       }
       KBatch kbB = kb;
       kbB.order = order + 3 * (size_t)stride;
-      kern<<<grid, nthr, pl.total_bytes, s>>>(h->kp, kbB, dstats, ncap, in_smem, gws, ctr + 7, ctr + 3);
+      kern<<<grid, nthr, pl.total_bytes, s>>>(h->kp, kbB, dstats, ncap, in_smem, gws, cnt + 3, ctr + 3);
       h->launches++;
       CK(cudaGetLastError());
     }
