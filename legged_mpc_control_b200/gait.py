@@ -58,3 +58,65 @@ def contact_table(horizon: int, dt: float, gait, phase, gait_speed):
             out[sel, :, leg] = predict_contact(int(g), leg, phase[sel, leg][:, None],
                                                gait_speed[sel][:, None], steps[None, :])
     return out
+
+
+class ContactFsm:
+    """Host mirror of the LeggedContactFSM state machine that drives the contact schedule
+    (LeggedContactFSM.cpp:16-36 reset, :38-84 update, :214-229 common_enter, :269-278 percent_in_state);
+    the swing-foot Bezier targets are not part of it.  Kept quirk for quirk: `update` TOGGLES stance/swing
+    at every transition instead of reading the pattern entry, so the three-entry legs of trot-with-stand /
+    crawl run their (STANCE, SWING, STANCE) table with alternating meaning, and the one-entry `stand`
+    pattern — whose index never wraps, so its phase is never brought back (:218-221) — leaves stance at
+    phase 1 for good.  The reference only ever activates the trot pattern (LeggedContactFSM.cpp:10).  The
+    device twin is fsm_update in csrc/lmpc_gait.h; tests compare both with the compiled reference."""
+
+    def __init__(self, gait: int, leg: int, gait_speed: float):
+        self.table = GAIT_TABLES[gait][leg]
+        self.speed = float(gait_speed)
+        self.reset()
+
+    def reset(self):
+        self.phase = 0.0
+        self.index = 0
+        self.start = 0.0
+        self.end = self.table[0][1]
+        self.state = self.table[0][0]
+
+    def percent(self):
+        with np.errstate(divide="ignore", invalid="ignore"):
+            p = np.float64(self.phase - self.start) / np.float64(self.end - self.start)
+        if p < 0.0:
+            p = np.float64(0.0)
+        elif p > 1.0:
+            p = np.float64(1.0)
+        return float(p)
+
+    def _enter(self):
+        prev = self.index
+        self.index = (self.index + 1) % len(self.table)
+        if self.index < prev:
+            self.phase -= 1.0
+        self.start = self.phase
+        self.end = self.table[self.index][1]
+
+    def update(self, dt: float, force_flag: bool = False):
+        self.phase += self.speed * dt
+        if self.state == 1:
+            if self.phase >= self.end:
+                self._enter()
+                self.state = 0
+        else:
+            pct = self.percent()
+            if (pct > 0.9 and force_flag) or pct >= 1.0:
+                self.state = 1
+                self._enter()
+        return self.phase
+
+    def predict(self, delta_t: float) -> int:
+        ph = self.phase + self.speed * delta_t
+        while ph > 1.0:
+            ph -= 1.0
+        for state, sw in self.table:
+            if ph <= sw:
+                return state
+        return 1

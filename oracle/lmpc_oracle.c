@@ -143,13 +143,13 @@ void orc_reference_trajectory(const lmpc_params* p, const double x0[12], const d
   for (int i = 0; i < 3; ++i)
     vw[i] = rot[i] * cmd[3] + rot[i + 3] * cmd[4] + rot[i + 6] * cmd[5];
   for (int i = 0; i < p->horizon; ++i) {
-    double t = p->dt * (double)(i + p->xref_index_offset);
+    const double k = (double)(i + p->xref_index_offset); /* evaluated as (rate * dt) * i, like :267-269 */
     double* xr = xref + NS * i; /* :264-276 */
     xr[0] = cmd[0];                 /* root_euler_d[0] */
     xr[1] = cmd[1];                 /* root_euler_d[1] */
-    xr[2] = x0[2] + cmd[8] * t;     /* fbk yaw + yaw rate_d * dt * i */
-    xr[3] = x0[3] + vw[0] * t;
-    xr[4] = x0[4] + vw[1] * t;
+    xr[2] = x0[2] + cmd[8] * p->dt * k; /* fbk yaw + yaw rate_d * dt * i */
+    xr[3] = x0[3] + vw[0] * p->dt * k;
+    xr[4] = x0[4] + vw[1] * p->dt * k;
     xr[5] = cmd[2];                 /* root_pos_d[2] */
     xr[6] = cmd[6];
     xr[7] = cmd[7];

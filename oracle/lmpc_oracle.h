@@ -4,14 +4,17 @@
  * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
  * load this library.  The product (liblmpc.so) never links or calls it.
  *
- * PARITY UNPINNED: the reference holds no test, fixture or golden vector for this path
- *  and its solve runs in OSQP + osqp-eigen, neither vendored nor
- * version-pinned (.devcontainer/Dockerfile:55,69), so the reference itself cannot be built or
- * run here (no Eigen, OSQP or ROS in this image).  This oracle restates the reference's
- * matrix construction line by line and solves the resulting QP EXACTLY (Goldfarb-Idnani dual
- * active set, KKT-verified) — parity is defined against the exact minimiser of the
- * reference's QP, which OSQP approximates to eps_abs=1e-3 / eps_rel=1e-4
- * (ConvexQPSolver.cpp:183-184).
+ * PINNED TO THE REFERENCE'S OWN CODE (construction) + exact solve.  The reference holds no test, fixture
+ * or golden vector for this path and its solve runs in OSQP + osqp-eigen, neither
+ * vendored nor version-pinned (.devcontainer/Dockerfile:55,69), an ADMM method stopped at eps_abs=1e-3 /
+ * eps_rel=1e-4 (ConvexQPSolver.cpp:183-184).  What IS pinned: oracle/_ref compiles the reference's
+ * unmodified ConvexQPSolver.cpp, ConvexMpc.cpp, LeggedContactFSM.cpp, LeggedState.cpp, Utils.cpp against
+ * header shims (oracle/shim) whose OsqpEigen stub captures the (P, q, A, l, u) handed to OSQP;
+ * tests/test_ref_pin.py shows orc_sparse_qp equals that capture bit for bit (<= 4 eps on the I_w^-1 [r]x
+ * entries) on 1024 states x 4 gaits, orc_gait_predict_contact equals predict_contact_state, and the exact
+ * minimiser of the captured QP equals this oracle's answer to 1e-9.  The solve itself is an exact
+ * Goldfarb-Idnani dual active-set method with a KKT certificate: parity is defined against the exact
+ * minimiser of the reference's QP, which OSQP only approximates.
  */
 #ifndef LMPC_ORACLE_H_
 #define LMPC_ORACLE_H_

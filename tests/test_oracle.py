@@ -251,14 +251,22 @@ def test_golden_fixtures_pin_the_oracle(oracle):
     active set and to 1e-9 in U by a fresh oracle build, and certified by the numpy twin."""
     gdir = os.path.join(os.path.dirname(__file__), "golden")
     files = sorted(f for f in os.listdir(gdir) if f.endswith(".npz"))
-    assert len(files) >= 3
+    assert len(files) >= 4 and "golden_refbuild_a1_h30.npz" in files
     for f in files:
         g = np.load(os.path.join(gdir, f))
         p = presets.preset(str(g["preset"]))
         batch = {k: g[k] for k in ("x0", "rot", "foot_pos_abs", "cmd", "contact")}
         out = oracle.solve_batch(p, batch, eliminate_swing=True)
         assert out["failures"] == 0
-        assert np.abs(out["U"] - g["U"]).max() < 1e-9
+        if "source" in g.files:  # tests/golden/make_golden_ref.py: minimiser of the QP the REFERENCE'S code built
+            assert str(g["source"]) == "oracle/_ref"
+            assert np.abs(out["U"] - g["U"]).max() <= 1e-9 * max(1.0, np.abs(g["U"]).max())
+            for i in range(len(g["x0"])):  # ... and the oracle's sparse QP reproduces the captured matrices' fingerprint
+                Pd, q, A, l, u = oracle.sparse_qp(p, batch, i)
+                fp = np.array([np.asarray(A).sum(), np.abs(np.asarray(A)).sum(), q.sum(), u[:12 * p.horizon].sum()])
+                assert np.allclose(fp, g["qp_fingerprint"][i], rtol=1e-13, atol=0), (f, i)
+        else:
+            assert np.abs(out["U"] - g["U"]).max() < 1e-9
         assert np.array_equal(out["active_set"], g["active_set"])
         x0, rot, foot, cmd, contact = oracle._one(batch, 0, p.horizon)
         Hn, gn, _, _ = on.condensed_qp(p, x0, rot, foot, cmd)
