@@ -1,15 +1,20 @@
 """GPU parity tests: liblmpc.so (through the C ABI) against the CPU oracle on identical seeded
-inputs.  Tolerances (BASELINE.json north_star): FP64 GRFs within 1e-6 relative, same active set."""
+inputs.  Tolerances (BASELINE.json north_star): FP64 GRFs within 1e-6 relative, same active set
+(rules in tests/parity_util.py)."""
+
 import os
+import sys
 
 import numpy as np
 import pytest
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 
 from legged_mpc_control_b200 import abi, presets, synth
 
 pytestmark = pytest.mark.gpu
 
-REL_TOL = 1e-6  # north_star: FP64 GRFs within 1e-6 relative of the exact solution
+from parity_util import REL_TOL, compare, norm_err as _rel_err  # noqa: E402
 
 
 def _engine(params, max_batch):
@@ -17,46 +22,16 @@ def _engine(params, max_batch):
     return ConvexMpcEngine(params, max_batch, device=0)
 
 
-def _rel_err(a, b):
-    scale = np.maximum(1.0, np.abs(b).max(axis=1))
-    return np.abs(a - b).max(axis=1) / scale
-
-
-def _active_mismatch(params, got, ref, U):
-    """Rows whose activity differs, ignoring rows whose oracle residual lies in the ambiguous
-    band [tol/10, 10 tol] (a tie within rounding of the tolerance, not a different active set)."""
-    H = params.horizon
-    diff = got["active_set"] ^ ref["active_set"]
-    bad = 0
-    for i in np.nonzero(diff.any(axis=1))[0]:
-        bits = np.nonzero(np.unpackbits(diff[i].view(np.uint8), bitorder="little"))[0]
-        f = U[i].reshape(H, 4, 3)
-        for bit in bits:
-            if bit < 16 * H:
-                k, leg, w = bit // 16, (bit % 16) // 4, bit % 4
-                fx, fy, fz = f[k, leg]
-                res = [fx + params.mu * fz, params.mu * fz - fx, fy + params.mu * fz, params.mu * fz - fy][w]
-            elif bit < 20 * H:
-                k, leg = (bit - 16 * H) // 4, (bit - 16 * H) % 4
-                res = f[k, leg, 2]
-            else:
-                k, leg = (bit - 20 * H) // 4, (bit - 20 * H) % 4
-                res = params.fz_max - f[k, leg, 2]
-            tol = params.active_tol
-            if not (tol / 10 <= abs(res) <= 10 * tol):
-                bad += 1
-    return bad
-
-
-def _check(params, batch, oracle, max_rel=REL_TOL):
+def _check(params, batch, oracle, max_rel=REL_TOL, label=None):
+    """CUDA path (through the C ABI) vs the oracle on the same inputs: element-wise 1e-6 on every
+    component of grf and U, 1e-9 norm-wise regression guard on exactly polished answers, identical
+    primal-active bitmask (ties within a decade of active_tol counted, reported and bounded)."""
     eng = _engine(params, len(batch["x0"]))
     got = eng.compute_grfs(batch)
     ref = oracle.solve_batch(params, batch, eliminate_swing=True)
     assert ref["failures"] == 0
-    assert (got["status"] <= abi.PROB_OK_IPM_ONLY).all(), np.bincount(got["status"])
-    assert _rel_err(got["grf"], ref["grf"]).max() <= max_rel
-    assert _rel_err(got["U"], ref["U"]).max() <= max_rel
-    assert _active_mismatch(params, got, ref, ref["U"]) == 0
+    rep = compare(params, got, ref, batch, rel_tol=max_rel)
+    print(f"[parity] {label or ''} {rep}")
     eng.close()
     return got, ref
 
