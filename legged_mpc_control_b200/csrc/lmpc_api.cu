@@ -8,37 +8,12 @@
 #include <string>
 #include <vector>
 
-#include "../../include/lmpc.h"
-#include "lmpc_solver.cuh"
-#include "lmpc_warp_solve.cuh"
-#include "lmpc_tile_solve.cuh"
+#include "lmpc_internal.h"
 #include "lmpc_rollout.cuh"
 
 namespace lmpc {
 
 // ---------------------------------------------------------------- kernels
-
-// Size classes by reduced dimension n (3 per stance leg-step):
-//   0: n <= 63            one warp per QP, 8 x 8 tiles        (solve_warp_kernel)
-//   1: 64 <= n <= 120     one warp per QP, 15 x 15 tiles      (solve_tile_kernel<15>)
-//   2: 121 <= n <= 192    one warp per QP, 24 x 24 tiles      (solve_tile_kernel<24>)
-//   4: 193 <= n <= 288    4 warps per QP, 36 x 36 tiles       (solve_tile_kernel<36>), factor in the global slot
-//   3: n > 288            4 warps per QP, 48 x 48 tiles       (solve_tile_kernel<48>); LMPC_CLS3=cta: scalar CTA kernel (solve_kernel)
-// Register cap of the one-warp kernel, measured on B200 (headline workload, solves/s):
-//   __launch_bounds__(32, 9): ptxas settles on 168 registers, 600 B of spills, 9 warps/SM   3.75 M
-//   __maxnreg__(224):         290 B of spills, 9 warps/SM                                   3.90 M
-//   __maxnreg__(255):         230 B of spills, 8 warps/SM                                   4.19 M
-// The kernel is latency-bound inside each warp, so fewer spills beat the ninth warp.
-#ifndef LMPC_WARP_MAXNREG
-#define LMPC_WARP_MAXNREG 255
-#endif
-constexpr int kNumClasses = 5;
-constexpr int kCtrCount = 8;  // counter block: work counters at [c], class sizes at [kCtrCount + c]
-constexpr int kTileA = 15, kTileB = 24, kTileC = 48;  // 8 x 48 = 384 = 12 x LMPC_MAX_HORIZON
-constexpr int kTileD = 36;  // class 4: 192 < n <= 288 (crawl at H = 30, stand at H = 20), same kernel as class 3
-__host__ __device__ inline int size_class(int n) {
-  return n <= 3 * WNBMAX ? 0 : (n <= 8 * kTileA ? 1 : (n <= 8 * kTileB ? 2 : (n <= 8 * kTileD ? 4 : 3)));
-}
 
 // Compacts the problems of every size class into its own index list (order + cls * B) with
 // warp-aggregated atomics; counts[cls] = size of the class; n_max of class 3 sizes its shared memory.
@@ -69,105 +44,6 @@ __global__ void classify_kernel(const uint8_t* __restrict__ contact, int H, int 
   if (lane == 0 && nB > 0) atomicMax(&stats->n_max, nB);
 }
 
-__device__ inline void flush_warp_stats(const WarpStats& ws, KStats* stats) {
-  if ((threadIdx.x & 31) == 0 && ws.problems) {
-    atomicAdd(&stats->problems, ws.problems);
-    atomicAdd(&stats->sum_n, ws.sum_n);
-    atomicAdd(&stats->sum_fact, ws.sum_fact);
-    atomicAdd(&stats->sum_polish, ws.sum_polish);
-    if (ws.not_ok) atomicAdd(&stats->not_ok, ws.not_ok);
-    if (ws.ipm_only) atomicAdd(&stats->ipm_only, ws.ipm_only);
-    if (ws.warm_hits) atomicAdd(&stats->warm_hits, ws.warm_hits);
-    atomicAdd(&stats->flops, ws.flops);
-  }
-}
-
-// Persistent solve for 64 <= n <= 8 NT, one QP per CTA of NW warps: fragment-ordered factor in shared
-// memory (61 KB at NT = 15, 154 KB at NT = 24), Hessian slot in the L2 workspace.  Warp 0 runs the
-// whole solve; warps 1 .. NW-1 only share the tile columns of every Cholesky factorization
-// (tile_helper_loop), which is where n >= 120 spends its time.
-template <int NT, int NW>
-__global__ void __maxnreg__(255) solve_tile_kernel(const __grid_constant__ KParams P,
-                                                             const __grid_constant__ KBatch Bt, KStats* stats,
-                                                             double* gws, const int* __restrict__ count,
-                                                             int* work_counter) {
-  extern __shared__ __align__(16) unsigned char smem[];
-  const TilePlan pl = make_tile_plan<NT>(P.H);
-  const size_t kSlot = tile_slot_doubles<NT>();
-  double* Hg = gws + (size_t)blockIdx.x * kSlot;
-  if (NW > 1 && threadIdx.x >= 32) {
-    tile_helper_loop<NT, NW>(P, pl, smem, Hg);
-    return;
-  }
-  const int lane = threadIdx.x;
-  const int total = *count;
-  WarpStats ws;
-  for (;;) {
-    int w = 0;
-    if (lane == 0) w = atomicAdd(work_counter, 1);
-    w = __shfl_sync(0xffffffffu, w, 0);
-    if (w >= total) break;
-    solve_one_tile<NT, NW>(P, Bt, ws, pl, smem, Hg, Bt.order[w]);
-  }
-  flush_warp_stats(ws, stats);
-  if (NW > 1) {
-    if (lane == 0) *tile_job() = 0;
-    __syncthreads();
-  }
-}
-
-// Persistent one-warp-per-QP solve (class A).  One warp per CTA: no block barrier exists in this
-// kernel.  Problems are handed out by an atomic counter; the scaled Hessian of the problem in
-// flight lives in this CTA's 32 KB slot of the L2-resident workspace `gws`.
-__global__ void __maxnreg__(LMPC_WARP_MAXNREG) solve_warp_kernel(const __grid_constant__ KParams P,
-                                                        const __grid_constant__ KBatch Bt,
-                                                        KStats* stats, double* gws,
-                                                        const int* __restrict__ count,
-                                                        int* work_counter) {
-  extern __shared__ __align__(16) unsigned char smem[];
-  const WarpPlan pl = make_warp_plan(P.H);
-  double* Hg = gws + (size_t)blockIdx.x * (WN * WN);
-  const int lane = threadIdx.x;
-  const int total = *count;
-  WarpStats ws;
-  for (;;) {
-    int w = 0;
-    if (lane == 0) w = atomicAdd(work_counter, 1);
-    w = __shfl_sync(0xffffffffu, w, 0);
-    if (w >= total) break;
-    solve_one_warp(P, Bt, ws, pl, smem, Hg, Bt.order[w]);
-  }
-  flush_warp_stats(ws, stats);
-}
-
-// Persistent solve: one CTA per QP at a time, problems handed out by an atomic counter.
-template <int NT>
-__global__ void __launch_bounds__(NT) solve_kernel(const __grid_constant__ KParams P,
-                                                   const __grid_constant__ KBatch Bt,
-                                                   KStats* stats, int ncap, int mats_in_smem,
-                                                   double* gws, const int* __restrict__ count,
-                                                   int* work_counter) {
-  extern __shared__ __align__(16) unsigned char smem[];
-  const SmemPlan pl = make_plan(P.H, ncap, mats_in_smem != 0);
-  double* gH = nullptr;
-  double* gM = nullptr;
-  if (!mats_in_smem) {
-    const size_t ps = (size_t)packed_size(ncap);
-    gH = gws + (size_t)blockIdx.x * 2 * ps;
-    gM = gH + ps;
-  }
-  int* si = reinterpret_cast<int*>(smem + pl.oINT);
-  for (;;) {
-    if (threadIdx.x == 0) si[INT_WORK] = atomicAdd(work_counter, 1);
-    __syncthreads();
-    const int w = si[INT_WORK];
-    __syncthreads();
-    if (w >= *count) break;
-    const int pi = Bt.order[w];
-    solve_one<NT>(P, Bt, stats, pl, smem, gH, gM, pi);
-  }
-}
-
 }  // namespace lmpc
 
 // ---------------------------------------------------------------- host side
@@ -177,38 +53,18 @@ using lmpc::KParams;
 using lmpc::KStats;
 
 static thread_local std::string g_err = "";
-static void set_err(const std::string& s) { g_err = s; }
+namespace lmpc { void set_err(const std::string& s) { g_err = s; } }
+using lmpc::set_err;
+using lmpc::DevBuf;
 extern "C" const char* lmpc_last_error_string(void) { return g_err.c_str(); }
 extern "C" int32_t lmpc_abi_version(void) { return LMPC_ABI_VERSION; }
 
-#define CK(call)                                                                              \
-  do {                                                                                        \
-    cudaError_t e_ = (call);                                                                  \
-    if (e_ != cudaSuccess) {                                                                  \
-      set_err(std::string(#call) + ": " + cudaGetErrorString(e_));                            \
-      return LMPC_ERR_CUDA;                                                                   \
-    }                                                                                         \
-  } while (0)
-
 static constexpr int kPackMax = 64;  // batches up to this size take the packed host path
-static constexpr int kThreads = 64;
-static constexpr int kThreadsSpill = 256;
-// Warps per QP of the tile classes, measured (C3 / reference preset, solves/s): NT=15: 598k / 647k / 519k at
-// 1 / 2 / 4 warps (4 warps cost the third CTA per SM); NT=24: 90k / 106k / 146k (one CTA per SM anyway).
-static constexpr int kTileWarpsA = 2, kTileWarpsB = 4;
 
-struct DevBuf {
-  void* p = nullptr;
-  size_t cap = 0;
-  cudaError_t ensure(size_t bytes) {
-    if (bytes <= cap) return cudaSuccess;
-    if (p) cudaFree(p);
-    p = nullptr; cap = 0;
-    cudaError_t e = cudaMalloc(&p, bytes);
-    if (e == cudaSuccess) cap = bytes;
-    return e;
-  }
-  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+// Experiment knobs, read ONCE per handle at lmpc_create (never on the solve path).
+struct Tuning {
+  int tile_nw = 0;        // LMPC_TILE_NW: warps per QP of tile classes 1/2 (0 = measured default)
+  bool debug_stats = false;  // LMPC_DEBUG_STATS: print per-solve counters to stderr
 };
 
 struct lmpc_handle {
@@ -233,8 +89,7 @@ struct lmpc_handle {
   // closed-loop rollout state (lmpc_rollout)
   DevBuf d_rx, d_rfw, d_rph, d_rgait, d_rspeed, d_rtot, d_xlog, d_glog;
   cudaEvent_t ev_r0 = nullptr, ev_r1 = nullptr;
-  cudaEvent_t ev_cls = nullptr;
-  int* h_cls = nullptr;  // pinned: n_max, |A|, |B|
+  Tuning tune;
   KStats last_stats;
   float last_ms = 0.f;
   int64_t launches = 0;
@@ -276,6 +131,8 @@ static void fill_kparams(const lmpc_params& p, KParams* k) {
   k->step_frac = 0.999; k->sigma_pow = 3;  // swept on the headline workload (tools/gpu_sweep2.sh): flat within 1 %, 0.999 leaves the fewest interior-point-only answers
   if (const char* e = getenv("LMPC_STEP_FRAC")) k->step_frac = atof(e);
   if (const char* e = getenv("LMPC_SIGMA_POW")) k->sigma_pow = atoi(e);
+  k->dual_rel = 1e-11;  // 1e-9 let multipliers of -1e-10 pass: amplified by cond(H) ~ 1e7 that moved late-horizon forces by 6e-6 relative (tests/test_gpu_parity_fullsize.py)
+  if (const char* e = getenv("LMPC_DUAL_REL")) k->dual_rel = atof(e);
   k->try_interior = p.solver == LMPC_SOLVER_ACTIVE_SET ? 1 : 0;
   if (const char* e = getenv("LMPC_TRY_INTERIOR")) k->try_interior = atoi(e);
   for (int i = 0; i < 9; ++i) k->inertia[i] = p.inertia[i];
@@ -284,6 +141,16 @@ static void fill_kparams(const lmpc_params& p, KParams* k) {
 
 extern "C" lmpc_status lmpc_set_warm_start(lmpc_handle* h, int32_t enable, int32_t horizon_shift);
 extern "C" void lmpc_destroy(lmpc_handle* h);
+
+static lmpc_status create_resources(lmpc_handle* h) {
+  CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+  CK(cudaEventCreate(&h->ev0));
+  CK(cudaEventCreate(&h->ev1));
+  CK(h->d_stats.ensure(sizeof(KStats)));
+  CK(h->d_counter.ensure(2 * lmpc::kCtrCount * sizeof(int)));  // work counters, class sizes
+  CK(h->d_order.ensure(lmpc::kNumClasses * (size_t)h->max_batch * sizeof(int)));
+  return LMPC_OK;
+}
 
 extern "C" lmpc_status lmpc_create(const lmpc_params* params, int32_t max_batch, int32_t device,
                                    lmpc_handle** out) {
@@ -298,7 +165,7 @@ extern "C" lmpc_status lmpc_create(const lmpc_params* params, int32_t max_batch,
     set_err(std::string("no CUDA device: this engine has no CPU fallback (") + cudaGetErrorString(e) + ")");
     return LMPC_ERR_NO_DEVICE;
   }
-  if (device < 0 || device >= ndev) { set_err("device ordinal out of range"); return LMPC_ERR_INVALID_ARG; }
+  if (device < 0 || device >= ndev || device >= lmpc::kMaxDevices) { set_err("device ordinal out of range"); return LMPC_ERR_INVALID_ARG; }
   CK(cudaSetDevice(device));
   cudaDeviceProp prop;
   CK(cudaGetDeviceProperties(&prop, device));
@@ -313,20 +180,18 @@ extern "C" lmpc_status lmpc_create(const lmpc_params* params, int32_t max_batch,
   h->max_batch = max_batch;
   h->num_sms = prop.multiProcessorCount;
   h->smem_optin = (int)prop.sharedMemPerBlockOptin;
-  CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
-  CK(cudaEventCreate(&h->ev0));
-  CK(cudaEventCreate(&h->ev1));
-  CK(cudaEventCreateWithFlags(&h->ev_cls, cudaEventDisableTiming));
-  CK(cudaMallocHost((void**)&h->h_cls, 4 * sizeof(int)));
-  CK(h->d_stats.ensure(sizeof(KStats)));
-  CK(h->d_counter.ensure(2 * lmpc::kCtrCount * sizeof(int)));  // work counters, class sizes
-  CK(h->d_order.ensure(lmpc::kNumClasses * (size_t)max_batch * sizeof(int)));
+  if (const char* e = getenv("LMPC_TILE_NW")) h->tune.tile_nw = atoi(e);
+  h->tune.debug_stats = getenv("LMPC_DEBUG_STATS") != nullptr;
   memset(&h->last_stats, 0, sizeof(KStats));
-  *out = h;
-  if (params->solver == LMPC_SOLVER_ACTIVE_SET) {  // the face records are this solver's state
-    lmpc_status ws = lmpc_set_warm_start(h, 1, 1);
-    if (ws != LMPC_OK) { lmpc_destroy(h); *out = nullptr; return ws; }
+  st = create_resources(h);
+  if (st == LMPC_OK && params->solver == LMPC_SOLVER_ACTIVE_SET) st = lmpc_set_warm_start(h, 1, 1);  // the face records are this solver's state
+  if (st != LMPC_OK) {  // nothing leaks: the handle, its stream, events and buffers go through lmpc_destroy
+    const std::string keep = g_err;
+    lmpc_destroy(h);
+    g_err = keep;
+    return st;
   }
+  *out = h;
   return LMPC_OK;
 }
 
@@ -341,53 +206,17 @@ extern "C" void lmpc_destroy(lmpc_handle* h) {
   for (DevBuf* b : bufs) b->release();
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
-  if (h->ev_cls) cudaEventDestroy(h->ev_cls);
   if (h->ev_r0) cudaEventDestroy(h->ev_r0);
   if (h->ev_r1) cudaEventDestroy(h->ev_r1);
-  if (h->h_cls) cudaFreeHost(h->h_cls);
   if (h->h_pin) cudaFreeHost(h->h_pin);
   if (h->h_pout) cudaFreeHost(h->h_pout);
   if (h->stream) cudaStreamDestroy(h->stream);
   delete h;
 }
 
-template <int NT, int NW>
-static lmpc_status launch_tile_nw(lmpc_handle* h, const KBatch& kb, cudaStream_t s, DevBuf* wsbuf, int* order, int* count,
-                                  int* work) {
-  const lmpc::TilePlan tp = lmpc::make_tile_plan<NT>(h->kp.H);
-  auto kern = lmpc::solve_tile_kernel<NT, NW>;
-  CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, tp.total_bytes));
-  int occ = 0;
-  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, 32 * NW, tp.total_bytes));
-  if (occ < 1) { set_err("tile solve kernel does not fit on an SM"); return LMPC_ERR_CUDA; }
-  int grid = h->num_sms * occ;
-  if (grid > kb.B) grid = kb.B;
-  const size_t slot = lmpc::tile_slot_doubles<NT>();
-  CK(wsbuf->ensure((size_t)grid * slot * sizeof(double)));
-  KBatch k = kb;
-  k.order = order;
-  kern<<<grid, 32 * NW, tp.total_bytes, s>>>(h->kp, k, (KStats*)h->d_stats.p, (double*)wsbuf->p, count, work);
-  h->launches++;
-  CK(cudaGetLastError());
-  return LMPC_OK;
-}
-// Warps per QP of the tile classes (LMPC_TILE_NW overrides for experiments: 1, 2 or 4).
-template <int NT>
-static lmpc_status launch_tile(lmpc_handle* h, const KBatch& kb, cudaStream_t s, DevBuf* wsbuf, int* order, int* count,
-                               int* work) {
-  int nw = NT == lmpc::kTileA ? kTileWarpsA : kTileWarpsB;
-  if (NT > lmpc::kTileB) return launch_tile_nw<NT, 4>(h, kb, s, wsbuf, order, count, work);
-  if (kb.B <= h->num_sms) nw = 4;  // fewer problems than SMs: latency counts, occupancy does not
-  if (const char* e = getenv("LMPC_TILE_NW")) nw = atoi(e);
-  if (nw == 1) return launch_tile_nw<NT, 1>(h, kb, s, wsbuf, order, count, work);
-  if (nw == 2) return launch_tile_nw<NT, 2>(h, kb, s, wsbuf, order, count, work);
-  return launch_tile_nw<NT, 4>(h, kb, s, wsbuf, order, count, work);
-}
-
-// Launch classify + the per-size-class solves on `s` for the device-resident batch `kb`.  The
-// one-warp-per-QP kernels are enqueued right behind the classification (they read their class
-// size on the device); the host only waits for the 16-byte read-back that sizes the CTA-per-QP
-// launch of the largest class, while the others run.
+// Launch classify + the per-size-class solves on `s` for the device-resident batch `kb`.  Every
+// solve kernel is enqueued right behind the classification and reads its class size on the device:
+// no host synchronisation.  A class is launched only if the horizon can produce it (n <= 12 H).
 static lmpc_status launch_solve(lmpc_handle* h, KBatch kb, cudaStream_t s) {
   const int H = h->kp.H;
   kb.warm = h->warm_enabled ? (uint8_t*)h->d_warm.p : nullptr;
@@ -396,89 +225,31 @@ static lmpc_status launch_solve(lmpc_handle* h, KBatch kb, cudaStream_t s) {
   int* ctr = (int*)h->d_counter.p;  // [c] work counters, [kCtrCount + c] class sizes
   int* cnt = ctr + lmpc::kCtrCount;
   int* order = (int*)h->d_order.p;  // class c at order + c * max_batch
-  const int stride = h->max_batch;
+  const size_t stride = (size_t)h->max_batch;
   CK(cudaMemsetAsync(dstats, 0, sizeof(KStats), s));
   CK(cudaMemsetAsync(ctr, 0, 2 * lmpc::kCtrCount * sizeof(int), s));
   CK(cudaEventRecord(h->ev0, s));
-  lmpc::classify_kernel<<<(kb.B + 255) / 256, 256, 0, s>>>(kb.contact, H, kb.B, dstats, order, stride, cnt);
+  lmpc::classify_kernel<<<(kb.B + 255) / 256, 256, 0, s>>>(kb.contact, H, kb.B, dstats, order, (int)stride, cnt);
   h->launches++;
-  const bool big = 12 * H > 8 * lmpc::kTileB;
-  static const bool cls3_cta = getenv("LMPC_CLS3") && !strcmp(getenv("LMPC_CLS3"), "cta");  // the scalar CTA kernel, kept for comparison
-  const bool may3 = big && cls3_cta;
-  if (may3) {
-    CK(cudaMemcpyAsync(h->h_cls, &dstats->n_max, sizeof(int), cudaMemcpyDeviceToHost, s));
-    CK(cudaMemcpyAsync(h->h_cls + 1, cnt + 3, sizeof(int), cudaMemcpyDeviceToHost, s));
-    CK(cudaEventRecord(h->ev_cls, s));
-  }
-  // ---- class 0: one warp per QP, 8 x 8 tiles
-  {
-    const lmpc::WarpPlan wp = lmpc::make_warp_plan(H);
-    auto kernA = lmpc::solve_warp_kernel;
-    CK(cudaFuncSetAttribute(kernA, cudaFuncAttributeMaxDynamicSharedMemorySize, wp.total_bytes));
-    int occ = 0;
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernA, 32, wp.total_bytes));
-    if (occ < 1) { set_err("warp solve kernel does not fit on an SM"); return LMPC_ERR_CUDA; }
-    int grid = h->num_sms * occ;
-    if (grid > kb.B) grid = kb.B;
-    CK(h->d_wsA.ensure((size_t)grid * lmpc::WN * lmpc::WN * sizeof(double)));
-    KBatch ka = kb;
-    ka.order = order;
-    kernA<<<grid, 32, wp.total_bytes, s>>>(h->kp, ka, dstats, (double*)h->d_wsA.p, cnt + 0, ctr + 0);
-    h->launches++;
-    CK(cudaGetLastError());
-  }
-  // ---- classes 1, 2: one warp per QP, 15 x 15 / 24 x 24 tiles (only if the horizon can reach them)
-  if (12 * H > 3 * lmpc::WNBMAX) {
-    lmpc_status st = launch_tile<lmpc::kTileA>(h, kb, s, &h->d_wsT1, order + stride, cnt + 1, ctr + 1);
+  const lmpc::LaunchCtx c{h->device, &h->kp, dstats, h->num_sms, s, &h->launches};
+  const int nmax = 12 * H;  // largest reduced dimension this horizon can produce
+  lmpc_status st = lmpc::launch_warp_class(c, kb, &h->d_wsA, order, cnt + 0, ctr + 0);
+  if (st != LMPC_OK) return st;
+  if (nmax > lmpc::kWarpNMax) {
+    st = lmpc::launch_tile15(c, kb, &h->d_wsT1, order + stride, cnt + 1, ctr + 1, h->tune.tile_nw);
     if (st != LMPC_OK) return st;
   }
-  if (12 * H > 8 * lmpc::kTileA) {
-    lmpc_status st = launch_tile<lmpc::kTileB>(h, kb, s, &h->d_wsT2, order + 2 * (size_t)stride, cnt + 2, ctr + 2);
+  if (nmax > 8 * lmpc::kTileA) {
+    st = lmpc::launch_tile24(c, kb, &h->d_wsT2, order + 2 * stride, cnt + 2, ctr + 2, h->tune.tile_nw);
     if (st != LMPC_OK) return st;
   }
-  if (big && !cls3_cta) {  // class 3 (n > 192): 48 x 48 tiles, 4 warps per QP, factor in the global workspace slot
-    lmpc_status st = launch_tile<lmpc::kTileC>(h, kb, s, &h->d_ws, order + 3 * (size_t)stride, cnt + 3, ctr + 3);
+  if (nmax > 8 * lmpc::kTileB) {  // class 4 (192 < n <= 288)
+    st = lmpc::launch_tile36(c, kb, &h->d_wsT3, order + 4 * stride, cnt + 4, ctr + 4, 0);
     if (st != LMPC_OK) return st;
   }
-  if (big) {  // class 4 (192 < n <= 288): 36 x 36 tiles, otherwise as class 3
-    lmpc_status st = launch_tile<lmpc::kTileD>(h, kb, s, &h->d_wsT3, order + 4 * (size_t)stride, cnt + 4, ctr + 4);
+  if (nmax > 8 * lmpc::kTileD) {  // class 3 (n > 288): only horizons above 24 reach it
+    st = lmpc::launch_tile48(c, kb, &h->d_ws, order + 3 * stride, cnt + 3, ctr + 3, 0);
     if (st != LMPC_OK) return st;
-  }
-  if (may3) {
-    CK(cudaEventSynchronize(h->ev_cls));
-    const int n_max = h->h_cls[0], countB = h->h_cls[1];
-    if (countB > 0) {
-      // ---- class 3: one CTA per QP; choose where the two packed matrices live
-      int ncap = n_max > 0 ? n_max : 3;
-      lmpc::SmemPlan pl = lmpc::make_plan(H, ncap, true);
-      int in_smem = 1;
-      if (pl.total_bytes > h->smem_optin) {
-        in_smem = 0;
-        pl = lmpc::make_plan(H, ncap, false);
-        if (pl.total_bytes > h->smem_optin) { set_err("shared-memory plan does not fit even with spilled matrices"); return LMPC_ERR_INVALID_ARG; }
-      }
-      // matrices in L2: latency bound, so more rows in flight per column (256 threads) pays
-      int nthr = in_smem ? kThreads : kThreadsSpill;
-      if (const char* e = getenv("LMPC_CLS3_THREADS")) nthr = atoi(e) == 64 ? 64 : (atoi(e) == 128 ? 128 : (atoi(e) == 512 ? 512 : 256));
-      auto kern = nthr == 64 ? lmpc::solve_kernel<64> : (nthr == 128 ? lmpc::solve_kernel<128> : (nthr == 512 ? lmpc::solve_kernel<512> : lmpc::solve_kernel<256>));
-      CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total_bytes));
-      int occ = 0;
-      CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, nthr, pl.total_bytes));
-      if (occ < 1) { set_err("solve kernel does not fit on an SM"); return LMPC_ERR_CUDA; }
-      int grid = h->num_sms * occ;
-      if (grid > countB) grid = countB;
-      double* gws = nullptr;
-      if (!in_smem) {
-        size_t bytes = (size_t)grid * 2 * lmpc::packed_size(ncap) * sizeof(double);
-        CK(h->d_ws.ensure(bytes));
-        gws = (double*)h->d_ws.p;
-      }
-      KBatch kbB = kb;
-      kbB.order = order + 3 * (size_t)stride;
-      kern<<<grid, nthr, pl.total_bytes, s>>>(h->kp, kbB, dstats, ncap, in_smem, gws, cnt + 3, ctr + 3);
-      h->launches++;
-      CK(cudaGetLastError());
-    }
   }
   CK(cudaEventRecord(h->ev1, s));
   return LMPC_OK;
@@ -488,7 +259,7 @@ static lmpc_status finish_solve(lmpc_handle* h, cudaStream_t s) {
   CK(cudaMemcpyAsync(&h->last_stats, h->d_stats.p, sizeof(KStats), cudaMemcpyDeviceToHost, s));
   CK(cudaStreamSynchronize(s));
   CK(cudaEventElapsedTime(&h->last_ms, h->ev0, h->ev1));
-  if (getenv("LMPC_DEBUG_STATS")) {
+  if (h->tune.debug_stats) {
     const KStats& k = h->last_stats;
     const double np = k.problems ? (double)k.problems : 1.0;
     fprintf(stderr, "[lmpc] problems %llu mean_n %.2f fact %.3f polish %.3f ipm_only %llu not_ok %llu kernel %.3f ms\n", k.problems,
@@ -707,6 +478,12 @@ extern "C" lmpc_status lmpc_rollout(lmpc_handle* h, int32_t batch, const lmpc_ro
   const size_t B = (size_t)batch, S = (size_t)cfg->steps;
   const bool dev = st->on_device != 0;
   if (!h->ev_r0) { CK(cudaEventCreate(&h->ev_r0)); CK(cudaEventCreate(&h->ev_r1)); }
+  // the rollout's warm-start mode is local to this call: the handle's own setting (lmpc_set_warm_start,
+  // or the ACTIVE_SET solver's) is put back on every exit path
+  struct WarmGuard {
+    lmpc_handle* h; bool en; int shift;
+    ~WarmGuard() { h->warm_enabled = en; h->warm_shift = shift; }
+  } warm_guard{h, h->warm_enabled, h->warm_shift};
   if (cfg->warm_start) {
     lmpc_status w = lmpc_set_warm_start(h, 1, 1);
     if (w != LMPC_OK) return w;

@@ -2,6 +2,8 @@
 // (lmpc_host.cpp) and the device gait scheduler (lmpc_rollout.cuh).  Reference citations are
 // relative to /root/reference/src/legged_ctrl/.
 #pragma once
+#include <math.h>
+
 #include "../../include/lmpc.h"
 
 #ifdef __CUDACC__
@@ -57,7 +59,13 @@ LMPC_HD inline int gait_predict(int gait, int leg, double phase, double gait_spe
 #else
   double ph = phase + gait_speed * delta_t;  // :281
 #endif
-  while (ph > 1.0) ph -= 1.0;                // :283-285
+  // :283-285 `while (ph > 1) ph -= 1`.  Every one of those subtractions is exact in binary floating
+  // point (the difference lies on ph's own ulp grid), so the loop equals ph - (ceil(ph) - 1) bit for
+  // bit — evaluated in O(1).  Where the reference's loop would never end (non-finite phase or speed;
+  // |ph| beyond 2^52, where ph - 1 == ph) the row falls through to its `should not reach here`
+  // STANCE instead of hanging the kernel.
+  if (!(ph == ph) || ph > 4503599627370496.0) return 1;
+  if (ph > 1.0) ph -= ceil(ph) - 1.0;
   for (int i = 0; i < t.n; ++i)              // :287-291
     if (ph <= t.sw[i]) return t.state[i];
   return 1;                                  // :293 "should not reach here" -> STANCE

@@ -1,0 +1,76 @@
+// lmpc_internal.h — host-side plumbing shared by the translation units of liblmpc.so: error
+// reporting, device buffers, size classes and the per-class launchers (each kernel family is
+// compiled in its own .cu so the library builds in parallel).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+
+#include "../../include/lmpc.h"
+#include "lmpc_types.cuh"
+
+namespace lmpc {
+
+void set_err(const std::string& s);
+
+#define CK(call)                                                                              \
+  do {                                                                                        \
+    cudaError_t e_ = (call);                                                                  \
+    if (e_ != cudaSuccess) {                                                                  \
+      ::lmpc::set_err(std::string(#call) + ": " + cudaGetErrorString(e_));                    \
+      return LMPC_ERR_CUDA;                                                                   \
+    }                                                                                         \
+  } while (0)
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  cudaError_t ensure(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e == cudaSuccess) cap = bytes;
+    return e;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+
+// Size classes by reduced dimension n (3 per stance leg-step):
+//   0: n <= 63            one warp per QP, 8 x 8 tiles        (solve_warp_kernel / solve_warp_f32_kernel)
+//   1: 64 <= n <= 120     15 x 15 tiles                       (solve_tile_kernel<15>)
+//   2: 121 <= n <= 192    24 x 24 tiles                       (solve_tile_kernel<24>)
+//   4: 193 <= n <= 288    36 x 36 tiles, factor in the global slot (solve_tile_kernel<36>)
+//   3: n > 288            48 x 48 tiles, factor in the global slot (solve_tile_kernel<48>)
+constexpr int kNumClasses = 5;
+constexpr int kCtrCount = 8;   // counter block: work counters at [c], class sizes at [kCtrCount + c]
+constexpr int kWarpNMax = 63;  // 3 * WNBMAX
+constexpr int kTileA = 15, kTileB = 24, kTileC = 48;  // 8 x 48 = 384 = 12 x LMPC_MAX_HORIZON
+constexpr int kTileD = 36;     // class 4: 192 < n <= 288 (crawl at H = 30, stand at H = 20)
+__host__ __device__ inline int size_class(int n) {
+  return n <= kWarpNMax ? 0 : (n <= 8 * kTileA ? 1 : (n <= 8 * kTileB ? 2 : (n <= 8 * kTileD ? 4 : 3)));
+}
+
+// What a per-class launcher needs from the handle.
+constexpr int kMaxDevices = 64;
+struct LaunchCtx {
+  int device;         // CUDA ordinal < kMaxDevices
+  const KParams* kp;
+  KStats* stats;      // device
+  int num_sms;
+  cudaStream_t stream;
+  int64_t* launches;  // host counter (bench evidence)
+};
+
+// Each launcher enqueues ONE persistent kernel that solves the problems listed in order[0 .. *count)
+// (count and the work counter live on the device; no host synchronisation).  `ws` is the launcher's
+// own L2-resident workspace, grown on demand.
+lmpc_status launch_warp_class(const LaunchCtx& c, const KBatch& kb, DevBuf* ws, const int* order, const int* count, int* work);
+// nw: warps per QP (1, 2 or 4; 0 = the measured default of the class)
+lmpc_status launch_tile15(const LaunchCtx& c, const KBatch& kb, DevBuf* ws, const int* order, const int* count, int* work, int nw);
+lmpc_status launch_tile24(const LaunchCtx& c, const KBatch& kb, DevBuf* ws, const int* order, const int* count, int* work, int nw);
+lmpc_status launch_tile36(const LaunchCtx& c, const KBatch& kb, DevBuf* ws, const int* order, const int* count, int* work, int nw);
+lmpc_status launch_tile48(const LaunchCtx& c, const KBatch& kb, DevBuf* ws, const int* order, const int* count, int* work, int nw);
+
+}  // namespace lmpc

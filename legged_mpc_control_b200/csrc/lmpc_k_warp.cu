@@ -1,0 +1,62 @@
+// lmpc_k_warp.cu — size class 0 (n <= 63): persistent one-warp-per-QP solve and its launcher.
+#include "lmpc_internal.h"
+#include "lmpc_warp_solve.cuh"
+
+namespace lmpc {
+
+// Register cap of the one-warp kernel, measured on B200 (headline workload, solves/s):
+//   __launch_bounds__(32, 9): ptxas settles on 168 registers, 600 B of spills, 9 warps/SM   3.75 M
+//   __maxnreg__(224):         290 B of spills, 9 warps/SM                                   3.90 M
+//   __maxnreg__(255):         230 B of spills, 8 warps/SM                                   4.19 M
+// The kernel is latency-bound inside each warp, so fewer spills beat the ninth warp.
+#ifndef LMPC_WARP_MAXNREG
+#define LMPC_WARP_MAXNREG 255
+#endif
+
+// One warp per CTA: no block barrier exists in this kernel.  Problems are handed out by an atomic
+// counter; the scaled Hessian of the problem in flight lives in this CTA's 32 KB slot of the
+// L2-resident workspace `gws`.
+__global__ void __maxnreg__(LMPC_WARP_MAXNREG) solve_warp_kernel(const __grid_constant__ KParams P,
+                                                        const __grid_constant__ KBatch Bt,
+                                                        KStats* stats, double* gws,
+                                                        const int* __restrict__ count,
+                                                        int* work_counter) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  const WarpPlan pl = make_warp_plan(P.H);
+  double* Hg = gws + (size_t)blockIdx.x * (WN * WN);
+  const int lane = threadIdx.x;
+  const int total = *count;
+  WarpStats ws;
+  for (;;) {
+    int w = 0;
+    if (lane == 0) w = atomicAdd(work_counter, 1);
+    w = __shfl_sync(0xffffffffu, w, 0);
+    if (w >= total) break;
+    solve_one_warp(P, Bt, ws, pl, smem, Hg, Bt.order[w]);
+  }
+  flush_warp_stats(ws, stats);
+}
+
+lmpc_status launch_warp_class(const LaunchCtx& c, const KBatch& kb, DevBuf* ws, const int* order, const int* count, int* work) {
+  const WarpPlan wp = make_warp_plan(c.kp->H);
+  static int occ_dev[kMaxDevices], bytes_dev[kMaxDevices];  // per device: the attribute lives in the device's context
+  int& occ_cached = occ_dev[c.device];
+  int& occ_bytes = bytes_dev[c.device];
+  if (occ_bytes != wp.total_bytes) {
+    CK(cudaFuncSetAttribute(solve_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, wp.total_bytes));
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_cached, solve_warp_kernel, 32, wp.total_bytes));
+    occ_bytes = wp.total_bytes;
+  }
+  if (occ_cached < 1) { set_err("warp solve kernel does not fit on an SM"); return LMPC_ERR_CUDA; }
+  int grid = c.num_sms * occ_cached;
+  if (grid > kb.B) grid = kb.B;
+  CK(ws->ensure((size_t)grid * WN * WN * sizeof(double)));
+  KBatch k = kb;
+  k.order = order;
+  solve_warp_kernel<<<grid, 32, wp.total_bytes, c.stream>>>(*c.kp, k, c.stats, (double*)ws->p, count, work);
+  ++*c.launches;
+  CK(cudaGetLastError());
+  return LMPC_OK;
+}
+
+}  // namespace lmpc

@@ -153,7 +153,7 @@ __global__ void rollout_step_kernel(const __grid_constant__ KParams P, const __g
   const double speed = D.gait_speed[p];
   for (int leg = 0; leg < 4; ++leg) {
     double ph = __dadd_rn(D.phase[4 * p + leg], __dmul_rn(speed, dt));  // LeggedContactFSM.cpp:50 (unfused)
-    while (ph > 1.0) ph -= 1.0;
+    if (ph > 1.0 && ph <= 4503599627370496.0) ph -= ceil(ph) - 1.0;  // == `while (ph > 1) ph -= 1` bit for bit (lmpc_gait.h), O(1)
     D.phase[4 * p + leg] = ph;
   }
   if (D.x_log) {

@@ -79,7 +79,7 @@ struct GmColumns<NT, 0, FROM_G> {
 // !FROM_G: M's lower tiles are already in Ls (diagonal tiles full symmetric).  On exit Ls holds
 // L_IJ (I > J) and inv(L_JJ) in the diagonal slots.  Returns false on a non-positive pivot.
 template <int NT, bool FROM_G>
-__device__ __noinline__ bool gm_factor(const double* Mg, double* Ls, double* xb, int nte) {
+static __device__ __noinline__ bool gm_factor(const double* Mg, double* Ls, double* xb, int nte) {
   const int lane = threadIdx.x & 31;
   double2* Lf = reinterpret_cast<double2*>(Ls) + lane;
   const double2* Mf = reinterpret_cast<const double2*>(Mg) + lane;
@@ -151,7 +151,7 @@ struct GmColumnsMW<NT, 0, FROM_G, NW, W> {
   __device__ static __forceinline__ bool run(const double2*, double2*, double*, int) { return false; }
 };
 template <int NT, bool FROM_G, int NW, int W>
-__device__ __noinline__ bool gm_factor_mw_w(const double* Mg, double* Ls, double* xb, int nte) {
+static __device__ __noinline__ bool gm_factor_mw_w(const double* Mg, double* Ls, double* xb, int nte) {
   const int lane = threadIdx.x & 31;
   double2* Lf = reinterpret_cast<double2*>(Ls) + lane;
   const double2* Mf = reinterpret_cast<const double2*>(Mg) + lane;
@@ -237,7 +237,7 @@ __device__ __forceinline__ void gm_solve_impl(const double* Ls, double* x, const
 }
 // nte = tiles this problem fills (<= NT).  The full-size case keeps its compile-time trip counts.
 template <int NT>
-__device__ __noinline__ void gm_solve(const double* Ls, double* x, int nte) {
+static __device__ __noinline__ void gm_solve(const double* Ls, double* x, int nte) {
   if (nte == NT) gm_solve_impl<NT>(Ls, x, NT);
   else gm_solve_impl<NT>(Ls, x, nte);
 }
@@ -266,7 +266,7 @@ __device__ __forceinline__ void gm_symv_impl(const double* Hg, const double* x, 
   }
 }
 template <int NT>
-__device__ __noinline__ void gm_symv(const double* Hg, const double* x, double* y, int nte, int i0 = 0, int di = 1) {
+static __device__ __noinline__ void gm_symv(const double* Hg, const double* x, double* y, int nte, int i0 = 0, int di = 1) {
   if (nte == NT) gm_symv_impl<NT>(Hg, x, y, NT, i0, di);
   else gm_symv_impl<NT>(Hg, x, y, nte, i0, di);
 }

@@ -431,7 +431,7 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
   gsinf = wmax(gsinf);
   const double rd_tol = 1e-9 * (gsinf > 1.0 ? gsinf : 1.0);
   const double rd_tol0 = P.rdtol0 * (gsinf > 1.0 ? gsinf : 1.0);
-  const double dual_tol = 1e-9 * (gsinf > sc ? gsinf : sc);
+  const double dual_tol = P.dual_rel * (gsinf > sc ? gsinf : sc);
   const double feas_tol = 1e-9;
   const int m = 5 * nb;
   const double inv_m = 1.0 / (double)m;
@@ -760,6 +760,29 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
       if (!any_changed) { polished = true; break; }
     }
     if (polished) {
+      // one step of iterative refinement on the verified face (see solve_one_warp): r = -T'(H u + g)
+      // on the free coordinates from the hu the verification just computed, factor still in Ls
+      for (int i = lane; i < N; i += 32) du[i] = 0.0;
+      __syncwarp();
+      for (int b = lane; b < nb; b += 32) {
+        const int sx = face[4 * b], sy = face[4 * b + 1], top = face[4 * b + 2], apex = face[4 * b + 3];
+        const double gx = gs[3 * b] + hu[3 * b], gy = gs[3 * b + 1] + hu[3 * b + 1], gz = gs[3 * b + 2] + hu[3 * b + 2];
+        const double gzt = gz + mu * (sx * gx + sy * gy);
+        du[3 * b] = (apex || sx != 0) ? 0.0 : -gx;
+        du[3 * b + 1] = (apex || sy != 0) ? 0.0 : -gy;
+        du[3 * b + 2] = (apex || top) ? 0.0 : -gzt;
+      }
+      __syncwarp();
+      gm_solve<NT>(Ls, du, nte);
+      __syncwarp();
+      for (int b = lane; b < nb; b += 32) {
+        const int sx = face[4 * b], sy = face[4 * b + 1];
+        const double vz = du[3 * b + 2];
+        dua[3 * b] += du[3 * b] + mu * sx * vz;
+        dua[3 * b + 1] += du[3 * b + 1] + mu * sy * vz;
+        dua[3 * b + 2] += vz;
+      }
+      __syncwarp();
       for (int i = lane; i < N; i += 32) u[i] = dua[i];
       __syncwarp();
       status = 0;

@@ -17,6 +17,7 @@ struct KParams {
   double rdtol0;  // relative dual-residual target of the first stage
   double fz0;     // initial fz as a fraction of fz_max (<= 0: m g / #stance legs of the step)
   double step_frac; // fraction of the step to the boundary (0.995)
+  double dual_rel;  // multiplier sign tolerance of the exact polish, relative to the gradient scale
   int sigma_pow;    // exponent of the Mehrotra centering rule (3)
   int try_interior; // experiment: cold problems first try the polish from all-interior faces
   double inertia[9];

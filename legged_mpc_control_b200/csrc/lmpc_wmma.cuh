@@ -209,8 +209,8 @@ __device__ __forceinline__ double2 wm_diag8_impl(double ax, double ay, double* x
   return make_double2(ra * ex, ra * ey);
 }
 // rolled (hot loop stays small in the instruction cache) and unrolled variants
-__device__ __noinline__ double2 wm_diag8(double ax, double ay, double* xb) { return wm_diag8_impl<true>(ax, ay, xb); }
-__device__ __noinline__ double2 wm_diag8u(double ax, double ay, double* xb) { return wm_diag8_impl<true>(ax, ay, xb); }
+static __device__ __noinline__ double2 wm_diag8(double ax, double ay, double* xb) { return wm_diag8_impl<true>(ax, ay, xb); }
+static __device__ __noinline__ double2 wm_diag8u(double ax, double ay, double* xb) { return wm_diag8_impl<true>(ax, ay, xb); }
 
 // Factor M = L L' (64 x 64, 8 x 8 tiles).  FROM_G: the lower tiles of M are read from the
 // full-symmetric fragment-ordered workspace Mg in global memory (L2; the interior-point loop keeps
@@ -221,7 +221,7 @@ __device__ __noinline__ double2 wm_diag8u(double ax, double ay, double* xb) { re
 // late columns the two k-chunks of a tile product accumulate in separate chains.
 // Returns false on a non-positive pivot.
 template <bool FROM_G>
-__device__ __noinline__ bool wm_factor(const double* Mg, double* Ls, double* xb) {
+static __device__ __noinline__ bool wm_factor(const double* Mg, double* Ls, double* xb) {
   const int lane = threadIdx.x & 31;
   double2* Lf = reinterpret_cast<double2*>(Ls) + lane;
   const double2* Mf = reinterpret_cast<const double2*>(Mg) + lane;
@@ -287,7 +287,7 @@ __device__ __noinline__ bool wm_factor(const double* Mg, double* Ls, double* xb)
 // substitution in t-layout: lane-local DFMA partials over the tiles of a block row, one ones-DMMA
 // per reduction (16 per triangular solve), straight-line code.
 // The caller must __syncwarp() between writing b and this call, and again before reading x.
-__device__ __noinline__ void wm_solve(const double* Ls, double* x) {
+static __device__ __noinline__ void wm_solve(const double* Ls, double* x) {
   const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   const double2* Lf = reinterpret_cast<const double2*>(Ls) + lane;
   const double* Lt = Ls + 16 * t + g;  // transposed reads: {Lt[64 T], Lt[64 T + 8]} = {T[2t][g], T[2t+1][g]}
@@ -335,7 +335,7 @@ __device__ __noinline__ void wm_solve(const double* Ls, double* x) {
 // y = H x for the full-symmetric fragment-ordered Hessian workspace (global, L2 resident);
 // x and y are 64-vectors in shared memory (x != y).  Caller syncs as for wm_solve.  Hg is
 // written earlier in the same kernel: loads go through L2 (__ldcg).
-__device__ __noinline__ void wm_symv(const double* Hg, const double* x, double* y) {
+static __device__ __noinline__ void wm_symv(const double* Hg, const double* x, double* y) {
   const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   const double2* Hf = reinterpret_cast<const double2*>(Hg) + lane;
   double2 xt[WNT];

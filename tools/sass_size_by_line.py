@@ -8,7 +8,7 @@ so, ksub = sys.argv[1:3]
 bucket = int(sys.argv[3]) if len(sys.argv) > 3 else 20
 rows = sass_lines(so, ksub)
 by = collections.Counter()
-for addr, loc, op in rows:
+for addr, loc, op, fn in rows:
     f, l = loc if loc else ("?", 0)
     by[(f, (l // bucket) * bucket)] += 16
 tot = sum(by.values())
