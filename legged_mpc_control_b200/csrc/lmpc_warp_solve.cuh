@@ -64,7 +64,7 @@ __device__ inline void flush_warp_stats(const WarpStats& ws, KStats* stats) {
 
 // 3x3 block (b1 >= b2 in block order, hence j1 >= j2) of cs*(B_qp' Qbar B_qp + Rbar), unscaled
 // by the cost normalisation.  out[a1 + 3*a2].
-__device__ __forceinline__ void wblock(int H, double dt2, double theta, double cs, double im2,
+static __device__ __noinline__ void wblock(int H, double dt2, double theta, double cs, double im2,
                                        const double* __restrict__ qw, const double* __restrict__ rw,
                                        const double* __restrict__ Bw, const double* __restrict__ cosv,
                                        const double* __restrict__ sinv, const double* __restrict__ Cs,
@@ -109,7 +109,8 @@ __device__ __forceinline__ void wblock(int H, double dt2, double theta, double c
 }
 
 __device__ __forceinline__ void pair_from_index(int pr, int& b1, int& b2) {
-  b1 = (int)((sqrt(8.0 * (double)pr + 1.0) - 1.0) * 0.5);
+  b1 = (int)((sqrtf(8.0f * (float)pr + 1.0f) - 1.0f) * 0.5f);  // float guess, fixed up exactly below (no FP64 sqrt slow path)
+  if (b1 < 0) b1 = 0;
   while (((b1 + 1) * (b1 + 2)) / 2 <= pr) ++b1;
   while ((b1 * (b1 + 1)) / 2 > pr) --b1;
   b2 = pr - (b1 * (b1 + 1)) / 2;

@@ -208,9 +208,64 @@ __device__ __forceinline__ double2 wm_diag8_impl(double ax, double ay, double* x
   }
   return make_double2(ra * ex, ra * ey);
 }
-// rolled (hot loop stays small in the instruction cache) and unrolled variants
+// Tensor-pipe variant of the same elimination (the default; -DLMPC_DIAG8_SMEM selects the
+// shared-memory one above).  Nothing travels through shared memory and there is no warp barrier:
+//   * a step only broadcasts the three numbers of its 2x2 pivot block P_s (three SHFLs); the
+//     multipliers X[g][0..1] = [A[g][2s] A[g][2s+1]] inv(P_s) are computed by the lanes that OWN
+//     those two elements (t == s) from their own registers;
+//   * the rank-2 updates are DMMAs whose k-slots are masked to slot s:  A -= X C'  uses the old
+//     A registers as the B operand (C = A[:, 2s..2s+1], by symmetry of the trailing matrix), and
+//     the inverse is accumulated TRANSPOSED, F = E':  F -= F[:, 2s..2s+1] X', so that both
+//     operands are again registers the lane already holds;
+//   * G' = F D' (2x2 Cholesky inverse of every pivot block, per-lane column pair) and one
+//     identity-DMMA pair transposes G' into the C-layout of G.
+// 16 DMMAs + 12 SHFLs per tile instead of ~400 instructions, and the F chain runs beside the A chain.
+__device__ __forceinline__ double2 wm_diag8_mma(double ax, double ay) {
+  const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  double fx = (g == 2 * t) ? 1.0 : 0.0, fy = (g == 2 * t + 1) ? 1.0 : 0.0;
+#pragma unroll
+  for (int s = 0; s < 3; ++s) {
+    const int src = 9 * s;  // lane (g = 2s, t = s)
+    const double a = __shfl_sync(0xffffffffu, ax, src);
+    const double b = __shfl_sync(0xffffffffu, ay, src);
+    const double d = __shfl_sync(0xffffffffu, ay, src + 4);
+    const double rdet = frcp(fma(a, d, -b * b));
+    const double c0 = ax, c1 = ay;
+    const bool act = (t == s) && (g > 2 * s + 1);
+    const double x0 = act ? -(fma(c0, d, -c1 * b) * rdet) : 0.0;   // -X[g][0]
+    const double x1 = act ? -(fma(c1, a, -c0 * b) * rdet) : 0.0;   // -X[g][1]
+    double2 A0 = make_double2(ax, ay), A1 = make_double2(0.0, 0.0);
+    dmma(A0, x0, c0);
+    dmma(A1, x1, c1);
+    double2 F0 = make_double2(fx, fy), F1 = make_double2(0.0, 0.0);
+    dmma(F0, fx, x0);
+    dmma(F1, fy, x1);
+    ax = A0.x + A1.x; ay = A0.y + A1.y;
+    fx = F0.x + F1.x; fy = F0.y + F1.y;
+  }
+  // final pivot block of this lane's column pair: rows 2t, 2t+1
+  const double a = __shfl_sync(0xffffffffu, ax, 9 * t);
+  const double b = __shfl_sync(0xffffffffu, ay, 9 * t);
+  const double d = __shfl_sync(0xffffffffu, ay, 9 * t + 4);
+  const double nan_ = __longlong_as_double(0x7ff8000000000000ll);
+  const double ra = (a > 0.0) ? frsqrt(a) : nan_;    // 1 / l11
+  const double ia = ra * ra;                         // 1 / a
+  const double sc = fma(-b * ia, b, d);              // l22^2 = d - b^2 / a
+  const double rs = (sc > 0.0) ? frsqrt(sc) : nan_;  // 1 / l22
+  const double gx = ra * fx;                         // G'[n][2t]   = G[2t][n]
+  const double gy = rs * fma(-(b * ia), fx, fy);     // G'[n][2t+1] = G[2t+1][n]
+  double2 G = make_double2(0.0, 0.0);
+  dmma(G, (g == 2 * t) ? 1.0 : 0.0, gx);
+  dmma(G, (g == 2 * t + 1) ? 1.0 : 0.0, gy);
+  return G;
+}
+#ifdef LMPC_DIAG8_SMEM
 static __device__ __noinline__ double2 wm_diag8(double ax, double ay, double* xb) { return wm_diag8_impl<true>(ax, ay, xb); }
 static __device__ __noinline__ double2 wm_diag8u(double ax, double ay, double* xb) { return wm_diag8_impl<true>(ax, ay, xb); }
+#else
+static __device__ __noinline__ double2 wm_diag8(double ax, double ay, double*) { return wm_diag8_mma(ax, ay); }
+static __device__ __noinline__ double2 wm_diag8u(double ax, double ay, double*) { return wm_diag8_mma(ax, ay); }
+#endif
 
 // Factor M = L L' (64 x 64, 8 x 8 tiles).  FROM_G: the lower tiles of M are read from the
 // full-symmetric fragment-ordered workspace Mg in global memory (L2; the interior-point loop keeps
