@@ -65,48 +65,69 @@ def workload_config(n_gpus, batch):
 
 
 # ------------------------------------------------------------------ CPU arm (oracle port)
-def cpu_sample(p, seconds_target=12.0, threads=None):
+def cpu_sample(p, seconds_target=12.0, threads=None, n_max=None, keep=False):
     """Times the oracle (the CPU restatement of the reference path; kind 'port') on a bounded
-    sample of the same workload with all host threads.  Returns (solves/s, cores, sample str)."""
+    sample of the same workload with all host threads: the first n problems of the stream, n sized
+    from a pilot so that the solve takes about `seconds_target` (capped at the batch).  The oracle
+    runs its swing-eliminated form (the reduced QP the GPU path solves; its condensing skips the
+    swing columns, so the baseline is not padded by work the solve discards).
+    Returns (solves/s, cores, sample str, n, seconds, outputs or None)."""
     from oracle import binding as ob
     ob.build()
     threads = threads or (os.cpu_count() or 1)
-    pilot_n = 32 * threads
+    n_max = n_max or BATCH
+    pilot_n = min(n_max, 32 * threads)
     _, b = make_workload(pilot_n, 0)
     t0 = time.perf_counter()
     ob.solve_batch(p, b, eliminate_swing=True, nthreads=threads, want_kkt=False)
     pilot = time.perf_counter() - t0
-    n = int(min(BATCH, max(pilot_n, pilot_n * seconds_target / max(pilot, 1e-3))))
+    n = int(min(n_max, max(pilot_n, pilot_n * seconds_target / max(pilot, 1e-3))))
     _, b = make_workload(n, 0)
     t0 = time.perf_counter()
     out = ob.solve_batch(p, b, eliminate_swing=True, nthreads=threads, want_kkt=False)
     dt = time.perf_counter() - t0
     assert out["failures"] == 0
-    return n / dt, threads, f"first {n} problems of the workload stream, {threads} threads, one problem per thread, {dt:.1f} s"
+    what = "the whole batch" if n == n_max else f"first {n} problems of the workload stream"
+    return (n / dt, threads, f"{what}, {threads} threads, one problem per thread, swing legs eliminated, {dt:.1f} s",
+            n, dt, (out, b) if keep else None)
 
 
 def run_reference(args):
-    """--impl reference: the reference's own implementation of this path cannot be built here
-    (Eigen + OSQP + ROS are absent), so this arm times the oracle port on the
-    host cores: rank 0 only."""
+    """--impl reference: the reference's own solver (OSQP through osqp-eigen) cannot be built here
+    (oracle/_ref compiles the reference's matrix construction against a capturing
+    OSQP stub, which has no solve), so this arm times the oracle port on the host cores: rank 0 only.
+    Every step solves the SAME bounded sample — the whole batch when the run fits in ~2.5 minutes —
+    and `ms_per_step` is the measured time of that step, `problems_per_step` its size."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    from oracle import binding as ob
     p = presets.preset(WORKLOADS[_WL][0])
-    vals = []
-    sample = ""
-    cores = os.cpu_count() or 1
-    for i in range(args.warmup + args.steps):
-        v, cores, sample = cpu_sample(p, seconds_target=args.cpu_seconds or max(2.0, 60.0 / (args.warmup + args.steps)))
+    n_steps = args.warmup + args.steps
+    budget = args.cpu_seconds * n_steps if args.cpu_seconds else 150.0
+    # size the per-step sample once, from a pilot
+    _, cores, _, n, dt, _ = cpu_sample(p, seconds_target=budget / n_steps, n_max=args.batch)
+    _, b = make_workload(n, 0)
+    times = []
+    for i in range(n_steps):
+        t0 = time.perf_counter()
+        out = ob.solve_batch(p, b, eliminate_swing=True, nthreads=cores, want_kkt=False)
+        t = time.perf_counter() - t0
+        assert out["failures"] == 0
         if i >= args.warmup:
-            vals.append(v)
-    val = float(np.mean(vals))
+            times.append(t)
+    step_s = float(np.mean(times))
+    val = n / step_s
+    what = "the whole batch" if n == args.batch else f"first {n} problems of the workload stream"
+    sample = f"{what} per step, {cores} threads, one problem per thread, swing legs eliminated, {step_s:.2f} s per step"
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * BATCH / val,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * step_s, "problems_per_step": n,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
-        "data": "synthetic", "config": workload_config(args.gpus, BATCH),
-        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "data": "synthetic", "config": workload_config(args.gpus, args.batch),
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample, "swing_eliminated": True,
+                         "what": "oracle/lmpc_oracle.c: reference QP construction restated (pinned bit-for-bit to oracle/_ref, the reference's own "
+                                 "ConvexQPSolver.cpp) + exact dual active-set solve; the reference's OSQP is not in this image"},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -269,7 +290,62 @@ def run_b200(args):
                      "what": "same workload, every solve warm-started from the stored faces of a copy of the batch moved by 1e-3 in x0"}
         eng.set_warm_start(False)
 
-    # ---- final result gather (the only exchange the path has; outside the timed region)
+    # ---- strong scaling (N > 1): the SAME global batch of 65 536 cut into N contiguous shards
+    strong_info = None
+    if world > 1:
+        Bs = B // world
+        _, sb = make_workload(Bs, rank * Bs)
+        sin_t = {k: torch.from_numpy(sb[k]).to(dev) for k in names}
+        spin = {k: v.data_ptr() for k, v in sin_t.items()}
+        for _ in range(3):
+            eng.solve_device(spin, pout, Bs, stream=stream, wait=True)
+        barrier()
+        sev = []
+        with torch.cuda.stream(ts):
+            for i in range(args.steps):
+                flush.fill_(i)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(ts)
+                eng.solve_device(spin, pout, Bs, stream=stream, wait=True)
+                e1.record(ts)
+                sev.append((e0, e1))
+        barrier()
+        sms = torch.tensor([sum(a.elapsed_time(b) for a, b in sev)], dtype=torch.float64, device=dev)
+        dist.all_reduce(sms, op=dist.ReduceOp.MAX)
+        strong_info = {"value": world * Bs * args.steps / (float(sms.item()) * 1e-3), "unit": UNIT, "global_batch": world * Bs,
+                       "batch_per_gpu": Bs, "ms_per_step": float(sms.item()) / args.steps,
+                       "limit": "persistent-grid tail: %d problems over %d resident warps per GPU (%.1f waves), plus the fixed classify + launch latency"
+                                % (Bs, 1184, Bs / 1184.0)}
+        barrier()
+
+    # ---- the product's single-process multi-GPU path (lmpc_solve_sharded: one host thread per
+    #      device inside liblmpc.so, host pointers, no NCCL), timed by rank 0 over all N devices
+    #      while the other ranks wait at the barrier
+    sharded_info = None
+    if rank == 0:
+        from legged_mpc_control_b200.engine import ShardedConvexMpcEngine
+        try:
+            sh = ShardedConvexMpcEngine(p, world * B, list(range(world)))
+            _, gb = make_workload(world * B, 0)
+            ghb = {k: torch.from_numpy(gb[k]).pin_memory().numpy() for k in names}
+            for _ in range(2):
+                sh.compute_grfs(ghb, copy=False)
+            t0 = time.perf_counter()
+            for _ in range(e2e_steps):
+                so = sh.compute_grfs(ghb, copy=False)
+            ssec = time.perf_counter() - t0
+            sharded_info = {"value": world * B * e2e_steps / ssec, "unit": UNIT, "devices": world, "steps": e2e_steps,
+                            "global_batch": world * B, "not_converged": so["not_converged"],
+                            "api": "ShardedConvexMpcEngine.compute_grfs -> lmpc_solve_sharded (host pointers, one thread per device, no NCCL)"}
+            sh.close()
+        except Exception as e:  # pragma: no cover
+            sharded_info = {"error": str(e)[:200]}
+    barrier()
+
+    eng.solve_device(pin, pout, B, stream=stream, wait=True)  # tout = cold answers of this rank's batch (parity + gather below)
+    bad = int((tout["status"] > 1).sum().item())
+
+    # ---- final result gather (the only exchange the path has; outside the timed region; through host memory, no NCCL)
     if world > 1:
         from legged_mpc_control_b200 import shard
         g = shard.gather_results(tout["grf"], world * B, rank, world)
@@ -291,7 +367,8 @@ def run_b200(args):
         Kf = stats["mean_factorizations"]
         f_alg_dense = 1728 * H * (H - 1) + 3456 * H * (H + 1) * (H + 2) / 6 + (2 * n * n + 24 * n) + Kf * (n ** 3 / 3 + 4 * n * n)
         io_bytes = B * (h2d / B + 12 * 8 + 4 + 4 + 4 * W)
-        cpu_val, cores, sample = cpu_sample(p)
+        cpu_val, cores, sample, n_cpu, _, kept = cpu_sample(p, keep=True)
+        parity = _parity(p, kept, tout, n_cpu)
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
@@ -316,7 +393,10 @@ def run_b200(args):
                 "hbm": {"algorithmic_bytes_per_launch": io_bytes, "achieved_GBps": io_bytes / (kms * 1e-3) / 1e9,
                         "peak_GBps": _hbm_peak()},
             },
-            "cpu_baseline": {"value": cpu_val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+            "cpu_baseline": {"value": cpu_val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample, "swing_eliminated": True},
+            "parity": parity,
+            "strong_scaling": strong_info,
+            "e2e_sharded_single_process": sharded_info,
             "not_converged": bad,
             "warm_start": warm_info,
         }
@@ -419,6 +499,22 @@ def run_c1(args):
                       "higher_is_better": False, "n_gpus": 1, "dtype": "f64", "data": "synthetic",
                       "config": {"workload": "c1_single_solve_batch1", "api": "ConvexMpcEngine.compute_grfs -> lmpc_solve (host pointers)"},
                       "presets": res}), flush=True)
+
+
+def _parity(p, kept, tout, n):
+    """CUDA results of the timed batch against the CPU oracle's answers for its first n problems
+    (the very problems cpu_baseline solved): tests/parity_util.py rules."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import parity_util as pu
+    ref, b = kept
+    got = {"grf": tout["grf"][:n].cpu().numpy(), "status": tout["status"][:n].cpu().numpy(),
+           "active_set": tout["active_set"][:n].cpu().numpy().view(np.uint32)}
+    bad, forgiven, rows = pu.active_mismatch(p, got["active_set"], ref["active_set"], ref["U"], b.get("mu"))
+    return {"problems": int(n), "against": "oracle (cpu_baseline's own outputs)",
+            "grf_max_rel_elementwise": float(pu.elem_err(got["grf"], ref["grf"]).max()),
+            "grf_max_rel_normwise": float(pu.norm_err(got["grf"], ref["grf"]).max()),
+            "active_mismatch_rows": bad, "active_tie_rows_forgiven": forgiven, "active_rows": rows,
+            "status_counts": np.bincount(got["status"], minlength=4).tolist(), "tolerance": pu.REL_TOL}
 
 
 def _ncu_traffic():

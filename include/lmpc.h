@@ -160,7 +160,8 @@ lmpc_status lmpc_create(const lmpc_params* params, int32_t max_batch, int32_t de
 
 /* Replaces calc_mpc_reference + update_cons_matrix + compute_grfs (ConvexMpc.cpp:70-72) for
  * `batch` independent robots.  Blocking.  Returns LMPC_ERR_NOT_CONVERGED if any problem failed
- * (its grf is zero, as the reference returns zeros on NaN); outputs are valid either way. */
+ * (its grf is zero, as the reference returns zeros on NaN); outputs are valid either way, and
+ * lmpc_last_not_converged gives the count. */
 lmpc_status lmpc_solve(lmpc_handle* h, int32_t batch, const lmpc_batch_in* in,
                        const lmpc_batch_out* out);
 
@@ -188,6 +189,25 @@ int64_t lmpc_last_warm_hits(const lmpc_handle* h);
 
 void lmpc_destroy(lmpc_handle* h);
 
+/* ---- one process, several GPUs (`devices[], n_devices`).  The batch is cut into
+ * contiguous index ranges [g B/G, (g+1) B/G), one engine and one host thread per device, NO
+ * collective and no NCCL: every QP is independent and the results land in disjoint slices of the
+ * caller's host arrays.  Host pointers only (pinned memory from lmpc_alloc_pinned gives full-rate
+ * copies on every device).  Warm-start records stay with the device that owns the slice: keep the
+ * batch order stable between ticks.  lmpc_solve_sharded returns LMPC_ERR_NOT_CONVERGED if any shard
+ * did; any other shard error is returned with its message (outputs of the other shards are valid). */
+typedef struct lmpc_sharded lmpc_sharded;
+lmpc_status lmpc_create_sharded(const lmpc_params* params, int32_t max_batch, const int32_t* devices,
+                                int32_t n_devices, lmpc_sharded** out);
+lmpc_status lmpc_solve_sharded(lmpc_sharded* s, int32_t batch, const lmpc_batch_in* in,
+                               const lmpc_batch_out* out);
+lmpc_status lmpc_set_warm_start_sharded(lmpc_sharded* s, int32_t enable, int32_t horizon_shift);
+int32_t lmpc_sharded_num_devices(const lmpc_sharded* s);
+lmpc_handle* lmpc_sharded_handle(lmpc_sharded* s, int32_t shard); /* the engine of one shard (stats, launch counts) */
+/* unconverged problems of the last lmpc_solve_sharded call, summed over the shards */
+int64_t lmpc_sharded_last_not_converged(const lmpc_sharded* s);
+void lmpc_destroy_sharded(lmpc_sharded* s);
+
 /* Page-locked host buffers for host-pointer lmpc_solve calls (full-rate H2D/D2H copies); plain
  * malloc'ed memory works too, just slower.  NULL on failure. */
 void* lmpc_alloc_pinned(size_t bytes);
@@ -197,6 +217,15 @@ void lmpc_free_pinned(void* p);
 const char* lmpc_last_error_string(void);
 
 int32_t lmpc_abi_version(void);
+
+/* Layout self-description for FFI bindings (ctypes, cgo, JNI): sizeof the struct `which` when
+ * field < 0, else offsetof its `field`-th member in declaration order; -1 if out of range.
+ * which: 0 lmpc_params, 1 lmpc_batch_in, 2 lmpc_batch_out, 3 lmpc_rollout_state,
+ * 4 lmpc_rollout_cfg, 5 lmpc_rollout_result. */
+int64_t lmpc_abi_sizeof(int32_t which, int32_t field);
+
+/* Problems of the last solve that ended with status >= 2 (grf zeroed). */
+int64_t lmpc_last_not_converged(const lmpc_handle* h);
 
 /* Kernel launches issued by this handle since creation (bench evidence). */
 int64_t lmpc_launch_count(const lmpc_handle* h);

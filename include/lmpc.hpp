@@ -16,7 +16,6 @@
 #include <stdexcept>
 #include <memory>
 #include <string>
-#include <thread>
 #include <utility>
 #include <vector>
 
@@ -105,11 +104,11 @@ class ConvexMpcEngine {
     return compute_grfs(t.x0, t.rot, t.foot_pos_abs, t.cmd, t.contact.data(), status);
   }
 
-  // Whole batch, SoA (see lmpc_batch_in).  Returns the number of problems that did not converge.
+  // Whole batch, SoA (see lmpc_batch_in).  Returns the number of problems that did not converge
+  // (their grf is zero, ConvexQPSolver.cpp:321-326).
   std::int64_t solve(int batch, const lmpc_batch_in& in, const lmpc_batch_out& out) {
-    const lmpc_status st = lmpc_solve(h_, batch, &in, &out);
-    detail::check(st, true);
-    return st == LMPC_ERR_NOT_CONVERGED ? 1 : 0;
+    detail::check(lmpc_solve(h_, batch, &in, &out), true);
+    return lmpc_last_not_converged(h_);
   }
   void solve_async(int batch, const lmpc_batch_in& in, const lmpc_batch_out& out, void* cuda_stream = nullptr) {
     detail::check(lmpc_solve_async(h_, batch, &in, &out, cuda_stream));
@@ -149,75 +148,36 @@ class ConvexMpcEngine {
   lmpc_handle* h_ = nullptr;
 };
 
-// One process, several GPUs: the batch is cut into contiguous index ranges
-// [g B/G, (g+1) B/G), one engine + one host thread per device, no collective — every QP is
-// independent and the results land in disjoint slices of the caller's output arrays.  Host pointers
-// only (each slice is staged by its own engine); warm-start records stay with the device that owns
-// the slice, so keep the batch order stable between ticks.
+// One process, several GPUs — thin wrapper of lmpc_create_sharded / lmpc_solve_sharded:
+// contiguous index ranges [g B/G, (g+1) B/G), one engine + one host thread per device, no collective.
+// Host pointers only; warm-start records stay with the device that owns the slice, so keep the batch
+// order stable between ticks.  All argument checks run in the C layer before any thread starts.
 class ShardedEngine {
  public:
   ShardedEngine(const lmpc_params& p, int max_batch, const std::vector<int>& devices) : params_(p) {
-    if (devices.empty()) throw Error(LMPC_ERR_INVALID_ARG, "lmpc: ShardedEngine needs at least one device");
-    const int G = (int)devices.size();
-    per_ = (max_batch + G - 1) / G;
-    for (int d : devices) engines_.emplace_back(new ConvexMpcEngine(p, per_, d));
+    std::vector<std::int32_t> d(devices.begin(), devices.end());
+    detail::check(lmpc_create_sharded(&params_, max_batch, d.data(), (std::int32_t)d.size(), &s_));
   }
-  int shards() const noexcept { return (int)engines_.size(); }
-  ConvexMpcEngine& shard(int g) { return *engines_[g]; }
+  ~ShardedEngine() { lmpc_destroy_sharded(s_); }
+  ShardedEngine(const ShardedEngine&) = delete;
+  ShardedEngine& operator=(const ShardedEngine&) = delete;
+  int shards() const noexcept { return lmpc_sharded_num_devices(s_); }
+  lmpc_handle* shard(int g) { return lmpc_sharded_handle(s_, g); }
   // first problem of shard g for a batch of B problems
   static int shard_begin(int B, int G, int g) { return (int)(((long long)B * g) / G); }
 
-  // Returns the number of shards that reported unconverged problems; rethrows the first hard error.
-  int solve(int batch, const lmpc_batch_in& in, const lmpc_batch_out& out) {
-    if (in.on_device || out.on_device) throw Error(LMPC_ERR_INVALID_ARG, "lmpc: ShardedEngine takes host pointers");
-    const int G = shards(), H = params_.horizon, W = LMPC_ACTIVE_WORDS(H);
-    std::vector<std::thread> th;
-    std::vector<int> rc(G, 0);
-    std::vector<std::string> err(G);
-    for (int g = 0; g < G; ++g) {
-      const int b0 = shard_begin(batch, G, g), b1 = shard_begin(batch, G, g + 1);
-      if (b1 <= b0) continue;
-      if (b1 - b0 > per_) throw Error(LMPC_ERR_INVALID_ARG, "lmpc: batch exceeds max_batch");
-      th.emplace_back([&, g, b0, b1] {
-        lmpc_batch_in i = in;
-        lmpc_batch_out o = out;
-        const size_t s = (size_t)b0;
-        i.x0 += 12 * s; i.rot += 9 * s; i.foot_pos_abs += 12 * s; i.cmd += 9 * s; i.contact += (size_t)(4 * H) * s;
-        if (i.q) i.q += 12 * s;
-        if (i.r) i.r += 12 * s;
-        if (i.mu) i.mu += s;
-        if (i.fz_max) i.fz_max += s;
-        if (i.mass) i.mass += s;
-        if (i.inertia) i.inertia += 9 * s;
-        o.grf += 12 * s;
-        if (o.status) o.status += s;
-        if (o.iters) o.iters += s;
-        if (o.active_set) o.active_set += (size_t)W * s;
-        if (o.U) o.U += (size_t)(12 * H) * s;
-        try {
-          rc[g] = (int)engines_[g]->solve(b1 - b0, i, o);
-        } catch (const Error& e) {
-          rc[g] = -1;
-          err[g] = e.what();
-        }
-      });
-    }
-    for (auto& t : th) t.join();
-    int unconverged = 0;
-    for (int g = 0; g < G; ++g) {
-      if (rc[g] < 0) throw Error(LMPC_ERR_CUDA, err[g]);
-      unconverged += rc[g];
-    }
-    return unconverged;
+  // Returns the number of problems that did not converge (their grf is zero); throws on any hard error.
+  std::int64_t solve(int batch, const lmpc_batch_in& in, const lmpc_batch_out& out) {
+    detail::check(lmpc_solve_sharded(s_, batch, &in, &out), /*allow_not_converged=*/true);
+    return lmpc_sharded_last_not_converged(s_);
   }
   void set_warm_start(bool enable, int horizon_shift = 1) {
-    for (auto& e : engines_) e->set_warm_start(enable, horizon_shift);
+    detail::check(lmpc_set_warm_start_sharded(s_, enable ? 1 : 0, horizon_shift));
   }
 
  private:
   lmpc_params params_;
-  int per_ = 0;
-  std::vector<std::unique_ptr<ConvexMpcEngine>> engines_;
+  lmpc_sharded* s_ = nullptr;
 };
 
 }  // namespace lmpc

@@ -14,7 +14,9 @@ EXPORTS = (
     "lmpc_reset_warm_start", "lmpc_destroy", "lmpc_last_error_string", "lmpc_abi_version",
     "lmpc_launch_count", "lmpc_last_kernel_ms", "lmpc_last_stats", "lmpc_gait_predict_contact",
     "lmpc_gait_contact_table", "lmpc_microbench_fp64", "lmpc_set_warm_start", "lmpc_last_warm_hits",
-    "lmpc_rollout", "lmpc_alloc_pinned", "lmpc_free_pinned",
+    "lmpc_rollout", "lmpc_alloc_pinned", "lmpc_free_pinned", "lmpc_last_not_converged",
+    "lmpc_create_sharded", "lmpc_solve_sharded", "lmpc_set_warm_start_sharded", "lmpc_sharded_num_devices",
+    "lmpc_sharded_handle", "lmpc_sharded_last_not_converged", "lmpc_destroy_sharded", "lmpc_abi_sizeof",
 )
 
 
@@ -59,6 +61,20 @@ def lib():
     L.lmpc_gait_predict_contact.restype = C.c_int32
     L.lmpc_gait_contact_table.argtypes = [C.c_int32, C.c_int32, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     L.lmpc_microbench_fp64.argtypes = [C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_double)]
+    L.lmpc_last_not_converged.argtypes = [C.c_void_p]
+    L.lmpc_last_not_converged.restype = C.c_int64
+    L.lmpc_create_sharded.argtypes = [C.POINTER(abi.LmpcParams), C.c_int32, C.POINTER(C.c_int32), C.c_int32, C.POINTER(C.c_void_p)]
+    L.lmpc_solve_sharded.argtypes = [C.c_void_p, C.c_int32, C.POINTER(abi.LmpcBatchIn), C.POINTER(abi.LmpcBatchOut)]
+    L.lmpc_set_warm_start_sharded.argtypes = [C.c_void_p, C.c_int32, C.c_int32]
+    L.lmpc_sharded_num_devices.argtypes = [C.c_void_p]
+    L.lmpc_sharded_handle.argtypes = [C.c_void_p, C.c_int32]
+    L.lmpc_sharded_handle.restype = C.c_void_p
+    L.lmpc_sharded_last_not_converged.argtypes = [C.c_void_p]
+    L.lmpc_sharded_last_not_converged.restype = C.c_int64
+    L.lmpc_destroy_sharded.argtypes = [C.c_void_p]
+    L.lmpc_destroy_sharded.restype = None
+    L.lmpc_abi_sizeof.argtypes = [C.c_int32, C.c_int32]
+    L.lmpc_abi_sizeof.restype = C.c_int64
     if L.lmpc_abi_version() != abi.ABI_VERSION:
         raise LmpcLibraryMissing(f"liblmpc.so ABI {L.lmpc_abi_version()} != python binding {abi.ABI_VERSION}")
     _LIB = L

@@ -1,6 +1,6 @@
 """ctypes mirror of include/lmpc.h (struct layouts and constants only; no code path).
 
-Kept byte-for-byte in step with the header; tests/test_abi.py checks sizeof/offsets against the
+Kept byte-for-byte in step with the header; tests/test_host.py::test_ctypes_mirror_matches_library_layout checks sizeof/offsets against the
 built library (lmpc_abi_version + a round trip through lmpc_params_preset).
 """
 import ctypes as C

@@ -5,7 +5,9 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <memory>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "lmpc_internal.h"
@@ -448,6 +450,116 @@ extern "C" void* lmpc_alloc_pinned(size_t bytes) {
   return p;
 }
 extern "C" void lmpc_free_pinned(void* p) { if (p) cudaFreeHost(p); }
+
+extern "C" int64_t lmpc_last_not_converged(const lmpc_handle* h) { return h ? (int64_t)h->last_stats.not_ok : 0; }
+
+// ---------------------------------------------------------------- one process, several GPUs
+struct lmpc_sharded {
+  lmpc_params params;
+  int per = 0;  // capacity of every shard
+  std::vector<lmpc_handle*> eng;
+  int64_t last_not_ok = 0;
+};
+
+extern "C" void lmpc_destroy_sharded(lmpc_sharded* s) {
+  if (!s) return;
+  for (lmpc_handle* h : s->eng) lmpc_destroy(h);
+  delete s;
+}
+
+extern "C" lmpc_status lmpc_create_sharded(const lmpc_params* params, int32_t max_batch, const int32_t* devices,
+                                           int32_t n_devices, lmpc_sharded** out) {
+  if (!out) { set_err("out is NULL"); return LMPC_ERR_INVALID_ARG; }
+  *out = nullptr;
+  if (!devices || n_devices < 1) { set_err("devices[] with n_devices >= 1 is required"); return LMPC_ERR_INVALID_ARG; }
+  if (max_batch < 1) { set_err("max_batch must be >= 1"); return LMPC_ERR_INVALID_ARG; }
+  if (!params) { set_err("params is NULL"); return LMPC_ERR_INVALID_ARG; }
+  lmpc_sharded* s = new lmpc_sharded();
+  s->params = *params;
+  s->per = (max_batch + n_devices - 1) / n_devices;  // ceil: floor-partitioned shards never exceed it
+  for (int g = 0; g < n_devices; ++g) {
+    lmpc_handle* h = nullptr;
+    const lmpc_status st = lmpc_create(params, s->per, devices[g], &h);
+    if (st != LMPC_OK) {
+      const std::string keep = g_err;
+      lmpc_destroy_sharded(s);
+      g_err = keep;
+      return st;
+    }
+    s->eng.push_back(h);
+  }
+  *out = s;
+  return LMPC_OK;
+}
+
+extern "C" int32_t lmpc_sharded_num_devices(const lmpc_sharded* s) { return s ? (int32_t)s->eng.size() : 0; }
+extern "C" lmpc_handle* lmpc_sharded_handle(lmpc_sharded* s, int32_t shard) {
+  return (s && shard >= 0 && shard < (int32_t)s->eng.size()) ? s->eng[shard] : nullptr;
+}
+extern "C" int64_t lmpc_sharded_last_not_converged(const lmpc_sharded* s) { return s ? s->last_not_ok : 0; }
+
+extern "C" lmpc_status lmpc_set_warm_start_sharded(lmpc_sharded* s, int32_t enable, int32_t horizon_shift) {
+  if (!s) { set_err("NULL handle"); return LMPC_ERR_INVALID_ARG; }
+  for (lmpc_handle* h : s->eng) {
+    const lmpc_status st = lmpc_set_warm_start(h, enable, horizon_shift);
+    if (st != LMPC_OK) return st;
+  }
+  return LMPC_OK;
+}
+
+extern "C" lmpc_status lmpc_solve_sharded(lmpc_sharded* s, int32_t batch, const lmpc_batch_in* in,
+                                          const lmpc_batch_out* out) {
+  if (!s || !in || !out) { set_err("NULL handle/in/out"); return LMPC_ERR_INVALID_ARG; }
+  if (in->on_device || out->on_device) { set_err("lmpc_solve_sharded takes host pointers"); return LMPC_ERR_INVALID_ARG; }
+  const int G = (int)s->eng.size();
+  // every argument check happens BEFORE the first thread starts: nothing can throw or return with
+  // joinable threads behind it
+  if (batch < 1 || (long long)batch > (long long)s->per * G) { set_err("batch must be in [1, max_batch]"); return LMPC_ERR_INVALID_ARG; }
+  if (!in->x0 || !in->rot || !in->foot_pos_abs || !in->cmd || !in->contact || !out->grf) {
+    set_err("x0, rot, foot_pos_abs, cmd, contact and out->grf are required"); return LMPC_ERR_INVALID_ARG;
+  }
+  const int H = s->params.horizon, W = LMPC_ACTIVE_WORDS(H);
+  auto begin = [&](int g) { return (int)(((long long)batch * g) / G); };
+  for (int g = 0; g < G; ++g)
+    if (begin(g + 1) - begin(g) > s->per) { set_err("shard larger than its engine (internal)"); return LMPC_ERR_INVALID_ARG; }
+  std::vector<lmpc_status> rc(G, LMPC_OK);
+  std::vector<std::string> err(G);
+  std::vector<std::thread> th;
+  th.reserve(G);
+  for (int g = 0; g < G; ++g) {
+    const int b0 = begin(g), b1 = begin(g + 1);
+    if (b1 <= b0) continue;
+    th.emplace_back([&, g, b0, b1] {
+      lmpc_batch_in i = *in;
+      lmpc_batch_out o = *out;
+      const size_t k = (size_t)b0;
+      i.x0 += 12 * k; i.rot += 9 * k; i.foot_pos_abs += 12 * k; i.cmd += 9 * k; i.contact += (size_t)(4 * H) * k;
+      if (i.q) i.q += 12 * k;
+      if (i.r) i.r += 12 * k;
+      if (i.mu) i.mu += k;
+      if (i.fz_max) i.fz_max += k;
+      if (i.mass) i.mass += k;
+      if (i.inertia) i.inertia += 9 * k;
+      o.grf += 12 * k;
+      if (o.status) o.status += k;
+      if (o.iters) o.iters += k;
+      if (o.active_set) o.active_set += (size_t)W * k;
+      if (o.U) o.U += (size_t)(12 * H) * k;
+      rc[g] = lmpc_solve(s->eng[g], b1 - b0, &i, &o);
+      if (rc[g] != LMPC_OK) err[g] = lmpc_last_error_string();  // thread-local: copy it out of the worker
+    });
+  }
+  for (auto& t : th) t.join();
+  s->last_not_ok = 0;
+  lmpc_status worst = LMPC_OK;
+  for (int g = 0; g < G; ++g) {
+    s->last_not_ok += lmpc_last_not_converged(s->eng[g]);
+    if (rc[g] == LMPC_OK) continue;
+    if (rc[g] != LMPC_ERR_NOT_CONVERGED || worst == LMPC_OK) { worst = rc[g]; set_err("shard " + std::to_string(g) + ": " + err[g]); }
+    if (rc[g] != LMPC_ERR_NOT_CONVERGED) break;
+  }
+  return worst;
+}
 
 extern "C" int64_t lmpc_launch_count(const lmpc_handle* h) { return h ? h->launches : 0; }
 extern "C" float lmpc_last_kernel_ms(const lmpc_handle* h) { return h ? h->last_ms : 0.f; }

@@ -1,5 +1,6 @@
 // lmpc_host.cpp — host-only parts of the C ABI: parameter presets and the gait schedule.
 // No CUDA here.  Reference citations are relative to /root/reference/src/legged_ctrl/.
+#include <stddef.h>
 #include <string.h>
 
 #include "../../include/lmpc.h"
@@ -62,4 +63,38 @@ extern "C" lmpc_status lmpc_gait_contact_table(int32_t batch, int32_t horizon, d
         contact[((size_t)b * horizon + i) * 4 + leg] =
             (uint8_t)lmpc_gait_predict_contact(gait[b], leg, phase[4 * (size_t)b + leg], gait_speed[b], (double)i * dt);
   return LMPC_OK;
+}
+
+// Layout self-description for FFI bindings (tests/test_host.py checks the ctypes mirror against it).
+extern "C" int64_t lmpc_abi_sizeof(int32_t which, int32_t field) {
+#define OFF(T, m) (int64_t) offsetof(T, m)
+  static const int64_t params[] = {OFF(lmpc_params, horizon), OFF(lmpc_params, discretisation), OFF(lmpc_params, cost_scaling),
+                                   OFF(lmpc_params, xref_index_offset), OFF(lmpc_params, precision), OFF(lmpc_params, solver),
+                                   OFF(lmpc_params, max_iter), OFF(lmpc_params, reserved0), OFF(lmpc_params, dt), OFF(lmpc_params, mu),
+                                   OFF(lmpc_params, fz_max), OFF(lmpc_params, mass), OFF(lmpc_params, gravity), OFF(lmpc_params, active_tol),
+                                   OFF(lmpc_params, inertia), OFF(lmpc_params, q), OFF(lmpc_params, r)};
+  static const int64_t bin[] = {OFF(lmpc_batch_in, x0), OFF(lmpc_batch_in, rot), OFF(lmpc_batch_in, foot_pos_abs), OFF(lmpc_batch_in, cmd),
+                                OFF(lmpc_batch_in, contact), OFF(lmpc_batch_in, q), OFF(lmpc_batch_in, r), OFF(lmpc_batch_in, mu),
+                                OFF(lmpc_batch_in, fz_max), OFF(lmpc_batch_in, mass), OFF(lmpc_batch_in, inertia), OFF(lmpc_batch_in, on_device),
+                                OFF(lmpc_batch_in, reserved0)};
+  static const int64_t bout[] = {OFF(lmpc_batch_out, grf), OFF(lmpc_batch_out, status), OFF(lmpc_batch_out, iters),
+                                 OFF(lmpc_batch_out, active_set), OFF(lmpc_batch_out, U), OFF(lmpc_batch_out, on_device),
+                                 OFF(lmpc_batch_out, reserved0)};
+  static const int64_t rst[] = {OFF(lmpc_rollout_state, x), OFF(lmpc_rollout_state, foot_world), OFF(lmpc_rollout_state, phase),
+                                OFF(lmpc_rollout_state, gait), OFF(lmpc_rollout_state, gait_speed), OFF(lmpc_rollout_state, cmd),
+                                OFF(lmpc_rollout_state, on_device), OFF(lmpc_rollout_state, reserved0)};
+  static const int64_t rcfg[] = {OFF(lmpc_rollout_cfg, steps), OFF(lmpc_rollout_cfg, warm_start), OFF(lmpc_rollout_cfg, default_foot_pos_rel),
+                                 OFF(lmpc_rollout_cfg, foot_delta_x_limit), OFF(lmpc_rollout_cfg, foot_delta_y_limit), OFF(lmpc_rollout_cfg, ground_z)};
+  static const int64_t rres[] = {OFF(lmpc_rollout_result, grf), OFF(lmpc_rollout_result, x_log), OFF(lmpc_rollout_result, grf_log),
+                                 OFF(lmpc_rollout_result, solves), OFF(lmpc_rollout_result, factorizations), OFF(lmpc_rollout_result, polish_rounds),
+                                 OFF(lmpc_rollout_result, not_converged), OFF(lmpc_rollout_result, warm_hits), OFF(lmpc_rollout_result, flops_executed),
+                                 OFF(lmpc_rollout_result, mean_n_eff), OFF(lmpc_rollout_result, device_ms), OFF(lmpc_rollout_result, reserved0)};
+#undef OFF
+  static const struct { const int64_t* off; int n; int64_t size; } tab[] = {
+      {params, (int)(sizeof(params) / 8), (int64_t)sizeof(lmpc_params)},         {bin, (int)(sizeof(bin) / 8), (int64_t)sizeof(lmpc_batch_in)},
+      {bout, (int)(sizeof(bout) / 8), (int64_t)sizeof(lmpc_batch_out)},          {rst, (int)(sizeof(rst) / 8), (int64_t)sizeof(lmpc_rollout_state)},
+      {rcfg, (int)(sizeof(rcfg) / 8), (int64_t)sizeof(lmpc_rollout_cfg)},        {rres, (int)(sizeof(rres) / 8), (int64_t)sizeof(lmpc_rollout_result)}};
+  if (which < 0 || which >= 6) return -1;
+  if (field < 0) return tab[which].size;
+  return field < tab[which].n ? tab[which].off[field] : -1;
 }

@@ -183,6 +183,60 @@ class ConvexMpcEngine:
             pass
 
 
+class ShardedConvexMpcEngine:
+    """One process, several GPUs (lmpc_create_sharded): contiguous index ranges, one engine and one
+    host thread per device inside liblmpc.so, no collective, host arrays in and out."""
+
+    def __init__(self, params: abi.LmpcParams, max_batch: int, devices):
+        self._L = _lib.lib()
+        self.params = params.copy()
+        self.devices = [int(d) for d in devices]
+        self._s = C.c_void_p()
+        self._pin_ptrs, self._pin_arrays, self._pin_key = [], None, None
+        arr = (C.c_int32 * len(self.devices))(*self.devices)
+        st = self._L.lmpc_create_sharded(C.byref(self.params), int(max_batch), arr, len(self.devices), C.byref(self._s))
+        if st != abi.OK:
+            raise LmpcError(st, _lib.last_error())
+
+    _pinned_out = ConvexMpcEngine._pinned_out
+    _free_pinned = ConvexMpcEngine._free_pinned
+
+    def compute_grfs(self, batch: dict, want_U: bool = False, copy: bool = True) -> dict:
+        H = self.params.horizon
+        sin, keep, nb = abi.host_batch_in(batch, H)
+        sout, out = abi.host_batch_out(nb, H, want_U, arrays=self._pinned_out(nb, want_U))
+        st = self._L.lmpc_solve_sharded(self._s, nb, C.byref(sin), C.byref(sout))
+        del keep
+        if st not in (abi.OK, abi.ERR_NOT_CONVERGED):
+            raise LmpcError(st, _lib.last_error())
+        if copy:
+            out = {k: v.copy() for k, v in out.items()}
+        out["rc"] = st
+        out["not_converged"] = int(self._L.lmpc_sharded_last_not_converged(self._s))
+        return out
+
+    def set_warm_start(self, enable: bool, horizon_shift: int = 1):
+        st = self._L.lmpc_set_warm_start_sharded(self._s, 1 if enable else 0, int(horizon_shift))
+        if st != abi.OK:
+            raise LmpcError(st, _lib.last_error())
+
+    @property
+    def launch_count(self) -> int:
+        return sum(int(self._L.lmpc_launch_count(self._L.lmpc_sharded_handle(self._s, g))) for g in range(len(self.devices)))
+
+    def close(self):
+        self._free_pinned()
+        if self._s:
+            self._L.lmpc_destroy_sharded(self._s)
+            self._s = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 def microbench_fp64(kind: int, device: int = 0, reps: int = 5) -> float:
     """TFLOP/s of the FP64 micro-kernel `kind` (include/lmpc_bench.h)."""
     out = C.c_double()

@@ -228,10 +228,15 @@ void orc_sparse_qp(const lmpc_params* p, const double x0[12], const double rot[9
   free(xref);
 }
 
-void orc_condensed_qp(const lmpc_params* p, const double x0[12], const double rot[9],
-                      const double foot[12], const double cmd[9], double* Hm, double* g,
-                      double* e_out) {
+/* `contact` (may be NULL): when given, the columns of swing legs are skipped — their entries of Hm
+ * and g stay untouched and are never read by the swing-eliminated solve.  The entries that ARE
+ * computed go through the same operations in the same order either way (bit-identical); skipping
+ * only keeps the timed CPU baseline (bench.py) from paying for columns the reduced QP discards. */
+static void condensed_qp_impl(const lmpc_params* p, const double x0[12], const double rot[9],
+                              const double foot[12], const double cmd[9], const uint8_t* contact,
+                              double* Hm, double* g, double* e_out) {
   const int H = p->horizon, n = 12 * H;
+#define COL_ON(c) (!contact || contact[4 * ((c) / 12) + ((c) % 12) / 3])
   const double cs = cost_scale(p);
   double* xref = (double*)malloc(sizeof(double) * NS * H);
   double* Ad = (double*)malloc(sizeof(double) * NS * NS * H);
@@ -258,12 +263,14 @@ void orc_condensed_qp(const lmpc_params* p, const double x0[12], const double ro
   }
   /* B_qp[k][j] = Ad_k ... Ad_{j+1} Bd_j  (rows of x_{k+1}, columns of u_j), k >= j */
   for (int j = 0; j < H; ++j) {
-    for (int c = 0; c < NU; ++c)
+    for (int c = 0; c < NU; ++c) {
+      if (!COL_ON(12 * j + c)) continue;
       for (int r = 0; r < NS; ++r) Bq[(12 * j + r) + (size_t)n * (12 * j + c)] = Bd[NS * NU * j + r + NS * c];
+    }
     for (int k = j + 1; k < H; ++k) {
       const double* A = Ad + NS * NS * k;
       for (int c = 0; c < NU; ++c)
-        for (int r = 0; r < NS; ++r) {
+        for (int r = 0; r < NS && COL_ON(12 * j + c); ++r) {
           double s = 0;
           for (int t = 0; t < NS; ++t) s += A[r + NS * t] * Bq[(12 * (k - 1) + t) + (size_t)n * (12 * j + c)];
           Bq[(12 * k + r) + (size_t)n * (12 * j + c)] = s;
@@ -272,7 +279,9 @@ void orc_condensed_qp(const lmpc_params* p, const double x0[12], const double ro
   }
   /* Hm = cs * (B_qp' Qbar B_qp + Rbar),  g = cs * B_qp' Qbar e */
   for (int c2 = 0; c2 < n; ++c2) {
+    if (!COL_ON(c2)) continue;
     for (int c1 = c2; c1 < n; ++c1) {
+      if (!COL_ON(c1)) continue;
       int kmin = (c1 / 12 > c2 / 12 ? c1 / 12 : c2 / 12);
       double s = 0;
       for (int row = 12 * kmin; row < n; ++row)
@@ -286,6 +295,13 @@ void orc_condensed_qp(const lmpc_params* p, const double x0[12], const double ro
   }
   if (e_out) memcpy(e_out, e, sizeof(double) * n);
   free(xref); free(Ad); free(Bd); free(cd); free(Bq); free(e);
+#undef COL_ON
+}
+
+void orc_condensed_qp(const lmpc_params* p, const double x0[12], const double rot[9],
+                      const double foot[12], const double cmd[9], double* Hm, double* g,
+                      double* e_out) {
+  condensed_qp_impl(p, x0, rot, foot, cmd, NULL, Hm, g, e_out);
 }
 
 /* ------------------------------------------------------------------ Goldfarb-Idnani */
@@ -525,7 +541,7 @@ int orc_solve(const lmpc_params* p, const double x0[12], const double rot[9],
   const double tol_act = p->active_tol > 0 ? p->active_tol : 1e-6;
   double* Hm = (double*)malloc(sizeof(double) * (size_t)n * n);
   double* g = (double*)malloc(sizeof(double) * n);
-  orc_condensed_qp(p, x0, rot, foot, cmd, Hm, g, NULL);
+  condensed_qp_impl(p, x0, rot, foot, cmd, eliminate_swing ? contact : NULL, Hm, g, NULL);
 
   /* variable map */
   int* var = (int*)malloc(sizeof(int) * n);   /* reduced -> full */

@@ -42,13 +42,17 @@ static int run_shard(char** argv) {
     lmpc_batch_out out{};
     in.x0 = x0.data(); in.rot = rot.data(); in.foot_pos_abs = foot.data(); in.cmd = cmd.data(); in.contact = contact.data();
     out.grf = grf.data(); out.status = status.data();
-    const int bad = eng.solve(B, in, out);
+    // a batch beyond the engine's capacity must come back as an exception from the argument check,
+    // before any shard thread starts (the old header threw with joinable threads alive)
+    int overflow_rejected = 0;
+    try { eng.solve(B + 3 * G, in, out); } catch (const lmpc::Error& e) { overflow_rejected = e.code() == LMPC_ERR_INVALID_ARG; }
+    const long long bad = eng.solve(B, in, out);
     std::ofstream o(argv[3], std::ios::binary);
     o.write(reinterpret_cast<const char*>(grf.data()), 8 * grf.size());
     o.write(reinterpret_cast<const char*>(status.data()), 4 * status.size());
     std::printf("shards %d devices", eng.shards());
     for (int d : devs) std::printf(" %d", d);
-    std::printf(" unconverged_shards %d\n", bad);
+    std::printf(" unconverged %lld overflow_rejected %d\n", bad, overflow_rejected);
     return 0;
   } catch (const lmpc::Error& e) {
     std::printf("lmpc::Error %d: %s\n", (int)e.code(), e.what());

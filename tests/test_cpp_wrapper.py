@@ -75,7 +75,7 @@ def test_sharded_engine_matches_oracle(wrapper_exe, oracle, tmp_path):
         f.write(np.ascontiguousarray(b["contact"], np.uint8).tobytes())
     r = subprocess.run([wrapper_exe, "shard", str(fin), str(fout), "northstar_a1", "3"], capture_output=True, text=True)
     assert r.returncode == 0, (r.returncode, r.stdout, r.stderr)
-    assert "shards 3" in r.stdout
+    assert "shards 3" in r.stdout and "overflow_rejected 1" in r.stdout and "unconverged 0" in r.stdout
     raw = open(fout, "rb").read()
     grf = np.frombuffer(raw[:B * 96], np.float64).reshape(B, 12)
     status = np.frombuffer(raw[B * 96:], np.int32)

@@ -10,7 +10,7 @@ import sys
 import numpy as np
 import pytest
 
-from legged_mpc_control_b200 import abi, gait, presets, shard, synth
+from legged_mpc_control_b200 import _lib, abi, gait, presets, shard, synth
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
@@ -197,3 +197,35 @@ def test_bench_reference_arm_contract(oracle):
     env = dict(os.environ, RANK="1", WORLD_SIZE="2")
     r1 = subprocess.run(cmd, capture_output=True, text=True, timeout=300, env=env)
     assert r1.returncode == 0 and r1.stdout.strip() == ""
+
+
+# ------------------------------------------------------------------ ABI layout
+def test_ctypes_mirror_matches_library_layout(lmpc_lib):
+    """sizeof and every offsetof of the ctypes structs in abi.py against what the built library
+    reports for include/lmpc.h (lmpc_abi_sizeof): a drifted field would silently shift pointers."""
+    import ctypes as C
+    structs = [abi.LmpcParams, abi.LmpcBatchIn, abi.LmpcBatchOut, abi.LmpcRolloutState, abi.LmpcRolloutCfg, abi.LmpcRolloutResult]
+    for which, S in enumerate(structs):
+        assert lmpc_lib.lmpc_abi_sizeof(which, -1) == C.sizeof(S), S.__name__
+        for i, (name, *_rest) in enumerate(S._fields_):
+            assert lmpc_lib.lmpc_abi_sizeof(which, i) == getattr(S, name).offset, (S.__name__, name)
+        assert lmpc_lib.lmpc_abi_sizeof(which, len(S._fields_)) == -1  # no field the mirror does not know about
+    assert lmpc_lib.lmpc_abi_sizeof(6, -1) == -1
+
+
+def test_gait_predict_never_hangs():
+    """the reference's `while (phase > 1) phase -= 1` never ends on inf / huge phase; the
+    O(1) wrap returns the reference's own fall-through (STANCE) there and is bit-identical otherwise."""
+    L = _lib.lib()
+    for ph, sp in ((np.inf, 1.0), (np.nan, 1.0), (0.3, np.inf), (1e300, 1.0), (0.5, 1e300)):
+        assert L.lmpc_gait_predict_contact(abi.GAIT_TROT, 1, float(ph), float(sp), 0.01) == 1
+    rng = np.random.default_rng(0)
+    for _ in range(2000):
+        ph, sp, dt = rng.uniform(0, 1), rng.uniform(0.5, 400.0), rng.uniform(0, 0.5)
+        x = ph + sp * dt
+        while x > 1.0:
+            x -= 1.0
+        g, leg = int(rng.integers(0, 6)), int(rng.integers(0, 4))
+        got = L.lmpc_gait_predict_contact(g, leg, ph, sp, dt)
+        assert got == int(gait.predict_contact(g, leg, ph, sp, dt))           # python twin (loops like the reference)
+        assert got == L.lmpc_gait_predict_contact(g, leg, x, 0.0, 0.0)        # the wrapped phase itself
