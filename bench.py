@@ -179,8 +179,10 @@ def run_b200(args):
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    host_group = None
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
+        host_group = dist.new_group(backend="gloo")  # host-side waits and the final gather: no NCCL kernel spins on a GPU meanwhile
 
     # weak scaling: rank r solves problems [r*B, (r+1)*B) of the stream
     B = args.batch
@@ -340,7 +342,9 @@ def run_b200(args):
             sh.close()
         except Exception as e:  # pragma: no cover
             sharded_info = {"error": str(e)[:200]}
-    barrier()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier(group=host_group)  # the other ranks wait here on the HOST: their GPUs are idle while rank 0 drives all N
 
     eng.solve_device(pin, pout, B, stream=stream, wait=True)  # tout = cold answers of this rank's batch (parity + gather below)
     bad = int((tout["status"] > 1).sum().item())
@@ -348,6 +352,7 @@ def run_b200(args):
     # ---- final result gather (the only exchange the path has; outside the timed region; through host memory, no NCCL)
     if world > 1:
         from legged_mpc_control_b200 import shard
+        shard._HOST_GROUP = host_group
         g = shard.gather_results(tout["grf"], world * B, rank, world)
         if rank == 0:
             assert g.shape[0] == world * B

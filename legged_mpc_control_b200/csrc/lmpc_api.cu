@@ -446,7 +446,8 @@ extern "C" int64_t lmpc_last_warm_hits(const lmpc_handle* h) { return h ? (int64
 // host-pointer lmpc_solve calls copy at full PCIe rate only from/to pinned buffers.
 extern "C" void* lmpc_alloc_pinned(size_t bytes) {
   void* p = nullptr;
-  if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) { set_err("cudaMallocHost failed"); return nullptr; }
+  // portable: pinned for EVERY device's context (lmpc_solve_sharded copies one array from several GPUs)
+  if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocPortable) != cudaSuccess) { set_err("cudaHostAlloc failed"); return nullptr; }
   return p;
 }
 extern "C" void lmpc_free_pinned(void* p) { if (p) cudaFreeHost(p); }

@@ -1,7 +1,7 @@
-// Drives include/lmpc.hpp and include/lmpc_legged_adapter.hpp (against the field-name mock of the
-// reference types) through liblmpc.so.  Prints one line per check; exit code 0 = all good,
-// 3 = no usable GPU (the engine refused to construct: there is no CPU fallback).
-//   argv[1] = "adapter": standing A1 through ConvexMpcB200::update -> prints the 12 GRFs
+// Drives include/lmpc.hpp (lmpc::ConvexMpcEngine, lmpc::ShardedEngine) through liblmpc.so.  Prints one
+// line per check; exit code 0 = all good, 3 = no usable GPU (the engine refused to construct: there is
+// no CPU fallback).  include/lmpc_legged_adapter.hpp is exercised by oracle/adapter_ref_main.cpp, which is
+// compiled against the reference's real headers (oracle/Makefile), not here.
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -9,7 +9,9 @@
 #include <fstream>
 #include <vector>
 
-#include "lmpc_legged_adapter.hpp"
+#include <array>
+
+#include "lmpc.hpp"
 
 // argv: shard <in.bin> <out.bin> <preset> <n_shards>: solve the batch of in.bin (int32 B, int32 H, then x0,
 // rot, foot_pos_abs, cmd as doubles and contact as bytes) through lmpc::ShardedEngine; shards sit
@@ -62,29 +64,30 @@ static int run_shard(char** argv) {
 
 int main(int argc, char** argv) {
   if (argc >= 6 && !std::strcmp(argv[1], "shard")) return run_shard(argv);
-  legged::LeggedState s;
+  // One reference-preset tick of a standing A1 in trot phase 0 through lmpc::ConvexMpcEngine, fed the way
+  // the adapter feeds it (x0, rot, foot_pos_abs, cmd, contact[H][4]); prints the 12 GRFs.
   const double q[12] = {60.0, 100.0, 0.0, 0.0, 0.0, 450.0, 0.15, 0.15, 100.0, 3.0, 3.0, 5.0};
-  for (int i = 0; i < 12; ++i) { s.param.q_weights[i] = q[i]; s.param.r_weights[i] = 1e-4; }
-  s.param.a1_trunk_inertia(0, 0) = 0.0158533; s.param.a1_trunk_inertia(1, 1) = 0.0377999; s.param.a1_trunk_inertia(2, 2) = 0.0456542;
-  s.fbk.root_pos[2] = 0.3; s.ctrl.root_pos_d[2] = 0.3;
-  for (int i = 0; i < 3; ++i) s.fbk.root_rot_mat(i, i) = 1.0;
+  double r[12];
+  for (int i = 0; i < 12; ++i) r[i] = 1e-4;
   const double fh[4][3] = {{0.17, 0.17, -0.3}, {0.17, -0.17, -0.3}, {-0.17, 0.17, -0.3}, {-0.17, -0.17, -0.3}};
-  for (int l = 0; l < 4; ++l)
-    for (int a = 0; a < 3; ++a) s.fbk.foot_pos_abs(a, l) = fh[l][a];
-  s.ctrl.plan_contacts[1] = s.ctrl.plan_contacts[2] = false;  // trot phase 0: legs 0 and 3 in stance
   try {
-    legged::ConvexMpcB200 mpc(s);
-    for (int tick = 0; tick < 3; ++tick) mpc.update(s, 0.01 * tick, 0.01);
-    std::printf("grf");
-    for (int i = 0; i < 12; ++i) std::printf(" %.17g", s.ctrl.optimized_input[i]);
-    std::printf("\n");
-    // direct use of the wrapper with a RobotTick and the gait helper
-    lmpc::ConvexMpcEngine eng(q, s.param.r_weights, "northstar_a1", 4);
+    lmpc::ConvexMpcEngine ref(q, r, "reference_a1", 1);
+    ref.set_warm_start(true, 1);
     lmpc::RobotTick t;
-    std::memcpy(t.x0.data() + 3, s.fbk.root_pos.data(), 24);
-    std::memcpy(t.rot.data(), s.fbk.root_rot_mat.data(), 72);
-    std::memcpy(t.foot_pos_abs.data(), s.fbk.foot_pos_abs.data(), 96);
-    t.cmd[2] = 0.3;
+    t.x0[5] = 0.3; t.cmd[2] = 0.3;
+    t.rot[0] = t.rot[4] = t.rot[8] = 1.0;
+    for (int l = 0; l < 4; ++l)
+      for (int a = 0; a < 3; ++a) t.foot_pos_abs[3 * l + a] = fh[l][a];
+    const double ph0[4] = {0.0, 0.0, 0.0, 0.0};
+    const auto c0 = ref.contact_table(LMPC_GAIT_TROT, ph0, 3.5);
+    std::memcpy(t.contact.data(), c0.data(), c0.size());
+    std::array<double, 12> grf{};
+    for (int tick = 0; tick < 3; ++tick) grf = ref.compute_grfs(t);  // ticks 2 and 3 start from the stored faces
+    std::printf("grf");
+    for (int i = 0; i < 12; ++i) std::printf(" %.17g", grf[i]);
+    std::printf("\n");
+    // the gait helper and a stand on the north-star preset
+    lmpc::ConvexMpcEngine eng(q, r, "northstar_a1", 4);
     const double ph[4] = {0.1, 0.1, 0.1, 0.1};
     const auto c = eng.contact_table(LMPC_GAIT_STAND, ph, 3.5);
     std::memcpy(t.contact.data(), c.data(), c.size());
