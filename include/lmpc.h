@@ -35,7 +35,7 @@
 extern "C" {
 #endif
 
-#define LMPC_ABI_VERSION 1
+#define LMPC_ABI_VERSION 2
 #define LMPC_MAX_HORIZON 32 /* reference PLAN_HORIZON is 30 (include/LeggedParams.h:13) */
 #define LMPC_NUM_LEG 4      /* include/LeggedParams.h:19, order FL FR RL RR */
 #define LMPC_STATE_DIM 12   /* MPC_STATE_DIM_SPARSE, include/LeggedParams.h:15 */
@@ -221,7 +221,7 @@ int32_t lmpc_abi_version(void);
 /* Layout self-description for FFI bindings (ctypes, cgo, JNI): sizeof the struct `which` when
  * field < 0, else offsetof its `field`-th member in declaration order; -1 if out of range.
  * which: 0 lmpc_params, 1 lmpc_batch_in, 2 lmpc_batch_out, 3 lmpc_rollout_state,
- * 4 lmpc_rollout_cfg, 5 lmpc_rollout_result. */
+ * 4 lmpc_rollout_cfg, 5 lmpc_rollout_result, 6 lmpc_fsm_io, 7 lmpc_leg_io, 8 lmpc_leg_geometry. */
 int64_t lmpc_abi_sizeof(int32_t which, int32_t field);
 
 /* Problems of the last solve that ended with status >= 2 (grf zeroed). */
@@ -276,6 +276,15 @@ typedef struct lmpc_rollout_state { /* one record per robot; all host or all dev
   const double* cmd;        /* [B][9]  as lmpc_batch_in.cmd */
   int32_t on_device;
   int32_t reserved0;
+  /* Optional (all four or none; same memory kind): the reference's contact STATE MACHINE
+   * (LeggedContactFSM::update, src/utils/LeggedContactFSM.cpp:38-84,214-229) instead of the stateless
+   * phase wrap — `phase` is then the FSM's unwrapped gait_phase, row 0 of the contact table is the
+   * FSM state (ctrl.plan_contacts, ConvexMpc.cpp:101-104) and rows i>0 are predicted from it.
+   * Initialise with lmpc_fsm_reset (or zeros + the pattern's first entry). */
+  int32_t* fsm_state;       /* [B][4] in/out  1 = STANCE, 0 = SWING */
+  int32_t* fsm_index;       /* [B][4] in/out  gait_pattern_index */
+  double* fsm_start;        /* [B][4] in/out  cur_state_start_time */
+  double* fsm_end;          /* [B][4] in/out  cur_state_end_time */
 } lmpc_rollout_state;
 
 typedef struct lmpc_rollout_cfg {
@@ -300,6 +309,78 @@ typedef struct lmpc_rollout_result {
 
 lmpc_status lmpc_rollout(lmpc_handle* h, int32_t batch, const lmpc_rollout_cfg* cfg,
                          const lmpc_rollout_state* state, lmpc_rollout_result* result);
+
+/* ---- batched contact state machine: LeggedContactFSM::reset / update for B robots x 4
+ * legs on the device.  All arrays [B][4] (gait, gait_speed [B]); host or device pointers, all of one
+ * kind.  foot_contact_flag may be NULL (no early-contact switch).  Outputs (either may be NULL):
+ * plan_contacts [B][4] = get_contact_state() after the update (ConvexMpc.cpp:101-104) and the solver's
+ * contact table [B][H][4] (row 0 = plan_contacts, row i = predict_contact_state(i*dt),
+ * ConvexQPSolver.cpp:329-346) for handle's horizon and MPC dt. ---- */
+typedef struct lmpc_fsm_io {
+  double* gait_phase;             /* in/out, unwrapped */
+  int32_t* fsm_state;             /* in/out */
+  int32_t* fsm_index;             /* in/out */
+  double* fsm_start;              /* in/out */
+  double* fsm_end;                /* in/out */
+  const int32_t* gait;            /* [B] LMPC_GAIT_* */
+  const double* gait_speed;       /* [B] */
+  const double* foot_contact_flag;/* [B][4] or NULL; != 0 means contact (LeggedState fbk.foot_contact_flag) */
+  uint8_t* plan_contacts;         /* [B][4] or NULL */
+  uint8_t* contact_table;         /* [B][H][4] or NULL */
+  int32_t on_device;
+  int32_t reserved0;
+} lmpc_fsm_io;
+lmpc_status lmpc_fsm_reset(lmpc_handle* h, int32_t batch, const lmpc_fsm_io* io);
+lmpc_status lmpc_fsm_update(lmpc_handle* h, int32_t batch, double dt, const lmpc_fsm_io* io);
+
+/* ---- batched GRF -> joint command stage: what the reference's low-level loop does with
+ * the MPC's output every 2.5 ms, for B robots at once.
+ *   lmpc_leg_kinematics  BaseInterface.cpp:280-300: foot_pos_rel = fk(q), J = jac(q), foot_vel_rel = J dq,
+ *                        foot_pos/vel_abs = R (.), foot_pos/vel_world (src/utils/A1Kinematics.cpp:8-18,42-140)
+ *   lmpc_tau_ctrl        BaseInterface::tau_ctrl_update, BaseInterface.cpp:451-500: tau = -J' R' f per leg;
+ *                        for movement_mode > 0 the joint angle target by the analytic inverse kinematics of the
+ *                        foot position target (A1Kinematics.cpp:321-446; NaN -> current angle) and the joint
+ *                        velocity target J^-1 R'(v_target - v_root) (NaN -> current velocity); otherwise the
+ *                        targets are the current joint state.
+ * Geometry: rho_fix[leg] = {offset_x, offset_y, motor_offset, upper_leg_length, lower_leg_length},
+ * rho_opt[leg] = calibration offsets (zero in the reference), BaseInterface.cpp:72-98.  Leg order FL FR RL RR.
+ * All arrays host or device pointers (one kind); outputs marked optional may be NULL. ---- */
+typedef struct lmpc_leg_geometry {
+  double rho_fix[4][5];
+  double rho_opt[4][3];
+} lmpc_leg_geometry;
+void lmpc_leg_geometry_a1(lmpc_leg_geometry* g); /* the reference's constants (LOWER_LEG_LENGTH = 0.21) */
+
+typedef struct lmpc_leg_io {
+  /* inputs */
+  const double* joint_pos;              /* [B][12] fbk.joint_pos */
+  const double* joint_vel;              /* [B][12] fbk.joint_vel */
+  const double* rot;                    /* [B][9]  fbk.root_rot_mat, column-major */
+  const double* root_pos;               /* [B][3] */
+  const double* root_lin_vel;           /* [B][3] */
+  const double* imu_ang_vel;            /* [B][3]  lmpc_leg_kinematics only (may be NULL -> zero) */
+  const double* grf;                    /* [B][12] ctrl.optimized_input[0:12]  (lmpc_tau_ctrl) */
+  const double* foot_pos_target_world;  /* [B][12] ctrl.optimized_state[6:18]  (lmpc_tau_ctrl) */
+  const double* foot_vel_target_world;  /* [B][12] ctrl.optimized_input[12:24] (lmpc_tau_ctrl) */
+  const double* movement_mode;          /* [B]     ctrl.movement_mode          (lmpc_tau_ctrl) */
+  /* outputs of lmpc_leg_kinematics (each optional) */
+  double* foot_pos_rel;                 /* [B][12] */
+  double* j_foot;                       /* [B][4][9] the four diagonal 3x3 blocks of fbk.j_foot, column-major */
+  double* foot_vel_rel;                 /* [B][12] */
+  double* foot_pos_abs;                 /* [B][12] */
+  double* foot_vel_abs;                 /* [B][12] */
+  double* foot_pos_world;               /* [B][12] */
+  double* foot_vel_world;               /* [B][12] */
+  /* outputs of lmpc_tau_ctrl */
+  double* joint_tau_tgt;                /* [B][12] */
+  double* joint_ang_tgt;                /* [B][12] in/out (the previous target is moved to prev_joint_ang_tgt) */
+  double* prev_joint_ang_tgt;           /* [B][12] optional */
+  double* joint_vel_tgt;                /* [B][12] */
+  int32_t on_device;
+  int32_t reserved0;
+} lmpc_leg_io;
+lmpc_status lmpc_leg_kinematics(lmpc_handle* h, int32_t batch, const lmpc_leg_geometry* g, const lmpc_leg_io* io);
+lmpc_status lmpc_tau_ctrl(lmpc_handle* h, int32_t batch, const lmpc_leg_geometry* g, const lmpc_leg_io* io);
 
 #ifdef __cplusplus
 }

@@ -17,6 +17,7 @@ EXPORTS = (
     "lmpc_rollout", "lmpc_alloc_pinned", "lmpc_free_pinned", "lmpc_last_not_converged",
     "lmpc_create_sharded", "lmpc_solve_sharded", "lmpc_set_warm_start_sharded", "lmpc_sharded_num_devices",
     "lmpc_sharded_handle", "lmpc_sharded_last_not_converged", "lmpc_destroy_sharded", "lmpc_abi_sizeof",
+    "lmpc_fsm_reset", "lmpc_fsm_update", "lmpc_leg_geometry_a1", "lmpc_leg_kinematics", "lmpc_tau_ctrl",
 )
 
 
@@ -73,6 +74,12 @@ def lib():
     L.lmpc_sharded_last_not_converged.restype = C.c_int64
     L.lmpc_destroy_sharded.argtypes = [C.c_void_p]
     L.lmpc_destroy_sharded.restype = None
+    L.lmpc_fsm_reset.argtypes = [C.c_void_p, C.c_int32, C.POINTER(abi.LmpcFsmIo)]
+    L.lmpc_fsm_update.argtypes = [C.c_void_p, C.c_int32, C.c_double, C.POINTER(abi.LmpcFsmIo)]
+    L.lmpc_leg_geometry_a1.argtypes = [C.POINTER(abi.LmpcLegGeometry)]
+    L.lmpc_leg_geometry_a1.restype = None
+    L.lmpc_leg_kinematics.argtypes = [C.c_void_p, C.c_int32, C.POINTER(abi.LmpcLegGeometry), C.POINTER(abi.LmpcLegIo)]
+    L.lmpc_tau_ctrl.argtypes = [C.c_void_p, C.c_int32, C.POINTER(abi.LmpcLegGeometry), C.POINTER(abi.LmpcLegIo)]
     L.lmpc_abi_sizeof.argtypes = [C.c_int32, C.c_int32]
     L.lmpc_abi_sizeof.restype = C.c_int64
     if L.lmpc_abi_version() != abi.ABI_VERSION:

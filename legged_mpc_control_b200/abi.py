@@ -7,7 +7,7 @@ import ctypes as C
 
 import numpy as np
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 MAX_HORIZON = 32
 NUM_LEG = 4
 
@@ -92,7 +92,27 @@ class LmpcRolloutState(C.Structure):
         ("cmd", C.c_void_p),
         ("on_device", C.c_int32),
         ("reserved0", C.c_int32),
+        ("fsm_state", C.c_void_p),
+        ("fsm_index", C.c_void_p),
+        ("fsm_start", C.c_void_p),
+        ("fsm_end", C.c_void_p),
     ]
+
+
+class LmpcFsmIo(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ("gait_phase", "fsm_state", "fsm_index", "fsm_start", "fsm_end", "gait", "gait_speed",
+                                          "foot_contact_flag", "plan_contacts", "contact_table")] + [("on_device", C.c_int32), ("reserved0", C.c_int32)]
+
+
+class LmpcLegIo(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in (
+        "joint_pos", "joint_vel", "rot", "root_pos", "root_lin_vel", "imu_ang_vel", "grf", "foot_pos_target_world", "foot_vel_target_world",
+        "movement_mode", "foot_pos_rel", "j_foot", "foot_vel_rel", "foot_pos_abs", "foot_vel_abs", "foot_pos_world", "foot_vel_world",
+        "joint_tau_tgt", "joint_ang_tgt", "prev_joint_ang_tgt", "joint_vel_tgt")] + [("on_device", C.c_int32), ("reserved0", C.c_int32)]
+
+
+class LmpcLegGeometry(C.Structure):
+    _fields_ = [("rho_fix", (C.c_double * 5) * 4), ("rho_opt", (C.c_double * 3) * 4)]
 
 
 class LmpcRolloutCfg(C.Structure):

@@ -63,42 +63,6 @@ extern "C" int32_t lmpc_abi_version(void) { return LMPC_ABI_VERSION; }
 
 static constexpr int kPackMax = 64;  // batches up to this size take the packed host path
 
-// Experiment knobs, read ONCE per handle at lmpc_create (never on the solve path).
-struct Tuning {
-  int tile_nw = 0;        // LMPC_TILE_NW: warps per QP of tile classes 1/2 (0 = measured default)
-  bool debug_stats = false;  // LMPC_DEBUG_STATS: print per-solve counters to stderr
-};
-
-struct lmpc_handle {
-  lmpc_params params;
-  KParams kp;
-  int device = 0;
-  int max_batch = 0;
-  int num_sms = 0;
-  int smem_optin = 0;
-  cudaStream_t stream = nullptr;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-  // device staging for host-pointer calls
-  DevBuf d_x0, d_rot, d_foot, d_cmd, d_contact, d_q, d_r, d_mu, d_fz, d_mass, d_inertia;
-  DevBuf d_grf, d_status, d_iters, d_active, d_U;
-  DevBuf d_stats, d_counter, d_ws, d_wsA, d_wsT1, d_wsT2, d_wsT3, d_order, d_warm;
-  bool warm_enabled = false;
-  int warm_shift = 1;
-  // small-batch host path: one packed H2D and one packed D2H (a single robot's tick is latency-bound)
-  DevBuf d_pin, d_pout;
-  unsigned char* h_pin = nullptr;
-  unsigned char* h_pout = nullptr;
-  // closed-loop rollout state (lmpc_rollout)
-  DevBuf d_rx, d_rfw, d_rph, d_rgait, d_rspeed, d_rtot, d_xlog, d_glog;
-  cudaEvent_t ev_r0 = nullptr, ev_r1 = nullptr;
-  Tuning tune;
-  KStats last_stats;
-  float last_ms = 0.f;
-  int64_t launches = 0;
-  bool pending = false;
-  cudaStream_t pending_stream = nullptr;
-};
-
 static lmpc_status validate_params(const lmpc_params* p) {
   if (!p) { set_err("params is NULL"); return LMPC_ERR_INVALID_ARG; }
   if (p->horizon < 1 || p->horizon > LMPC_MAX_HORIZON) { set_err("horizon out of range [1, 32]"); return LMPC_ERR_INVALID_ARG; }
@@ -204,7 +168,7 @@ extern "C" void lmpc_destroy(lmpc_handle* h) {
   DevBuf* bufs[] = {&h->d_x0, &h->d_rot, &h->d_foot, &h->d_cmd, &h->d_contact, &h->d_q, &h->d_r, &h->d_mu,
                     &h->d_fz, &h->d_mass, &h->d_inertia, &h->d_grf, &h->d_status, &h->d_iters, &h->d_active,
                     &h->d_U, &h->d_stats, &h->d_counter, &h->d_ws, &h->d_wsA, &h->d_wsT1, &h->d_wsT2, &h->d_wsT3, &h->d_order, &h->d_warm,
-                    &h->d_pin, &h->d_pout, &h->d_rx, &h->d_rfw, &h->d_rph, &h->d_rgait, &h->d_rspeed, &h->d_rtot, &h->d_xlog, &h->d_glog};
+                    &h->d_pin, &h->d_pout, &h->d_rx, &h->d_rfw, &h->d_rph, &h->d_rgait, &h->d_rspeed, &h->d_rtot, &h->d_xlog, &h->d_glog, &h->d_rfsm};
   for (DevBuf* b : bufs) b->release();
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
@@ -612,9 +576,14 @@ extern "C" lmpc_status lmpc_rollout(lmpc_handle* h, int32_t batch, const lmpc_ro
   lmpc::RolloutDev D;
   memset(&D, 0, sizeof(D));
   const double* d_cmd = st->cmd;
+  const bool fsm = st->fsm_state || st->fsm_index || st->fsm_start || st->fsm_end;
+  if (fsm && !(st->fsm_state && st->fsm_index && st->fsm_start && st->fsm_end)) {
+    set_err("fsm_state, fsm_index, fsm_start, fsm_end: give all four or none"); return LMPC_ERR_INVALID_ARG;
+  }
   if (dev) {
     D.x = st->x; D.foot_world = st->foot_world; D.phase = st->phase; D.gait = st->gait; D.gait_speed = st->gait_speed;
     D.x_log = res->x_log; D.grf_log = res->grf_log;
+    D.fsm_state = st->fsm_state; D.fsm_index = st->fsm_index; D.fsm_start = st->fsm_start; D.fsm_end = st->fsm_end;
   } else {
     CK(h->d_rx.ensure(B * 12 * 8)); CK(h->d_rfw.ensure(B * 12 * 8)); CK(h->d_rph.ensure(B * 4 * 8));
     CK(h->d_rgait.ensure(B * 4)); CK(h->d_rspeed.ensure(B * 8)); CK(h->d_cmd.ensure(B * 9 * 8));
@@ -627,6 +596,15 @@ extern "C" lmpc_status lmpc_rollout(lmpc_handle* h, int32_t batch, const lmpc_ro
     D.x = (double*)h->d_rx.p; D.foot_world = (double*)h->d_rfw.p; D.phase = (double*)h->d_rph.p;
     D.gait = (const int*)h->d_rgait.p; D.gait_speed = (const double*)h->d_rspeed.p;
     d_cmd = (const double*)h->d_cmd.p;
+    if (fsm) {  // [state | index | start | end], 4 B entries each
+      CK(h->d_rfsm.ensure(B * 4 * (4 + 4 + 8 + 8)));
+      unsigned char* f = (unsigned char*)h->d_rfsm.p;
+      D.fsm_state = (int*)f; D.fsm_index = (int*)(f + B * 16); D.fsm_start = (double*)(f + B * 32); D.fsm_end = (double*)(f + B * 64);
+      CK(cudaMemcpyAsync(D.fsm_state, st->fsm_state, B * 16, cudaMemcpyHostToDevice, s));
+      CK(cudaMemcpyAsync(D.fsm_index, st->fsm_index, B * 16, cudaMemcpyHostToDevice, s));
+      CK(cudaMemcpyAsync(D.fsm_start, st->fsm_start, B * 32, cudaMemcpyHostToDevice, s));
+      CK(cudaMemcpyAsync(D.fsm_end, st->fsm_end, B * 32, cudaMemcpyHostToDevice, s));
+    }
     if (res->x_log) { CK(h->d_xlog.ensure(S * B * 12 * 8)); D.x_log = (double*)h->d_xlog.p; }
     if (res->grf_log) { CK(h->d_glog.ensure(S * B * 12 * 8)); D.grf_log = (double*)h->d_glog.p; }
   }
@@ -662,6 +640,12 @@ extern "C" lmpc_status lmpc_rollout(lmpc_handle* h, int32_t batch, const lmpc_ro
     CK(cudaMemcpyAsync(st->x, D.x, B * 12 * 8, cudaMemcpyDeviceToHost, s));
     CK(cudaMemcpyAsync(st->foot_world, D.foot_world, B * 12 * 8, cudaMemcpyDeviceToHost, s));
     CK(cudaMemcpyAsync(st->phase, D.phase, B * 4 * 8, cudaMemcpyDeviceToHost, s));
+    if (fsm) {
+      CK(cudaMemcpyAsync(st->fsm_state, D.fsm_state, B * 16, cudaMemcpyDeviceToHost, s));
+      CK(cudaMemcpyAsync(st->fsm_index, D.fsm_index, B * 16, cudaMemcpyDeviceToHost, s));
+      CK(cudaMemcpyAsync(st->fsm_start, D.fsm_start, B * 32, cudaMemcpyDeviceToHost, s));
+      CK(cudaMemcpyAsync(st->fsm_end, D.fsm_end, B * 32, cudaMemcpyDeviceToHost, s));
+    }
     if (res->x_log) CK(cudaMemcpyAsync(res->x_log, D.x_log, S * B * 12 * 8, cudaMemcpyDeviceToHost, s));
     if (res->grf_log) CK(cudaMemcpyAsync(res->grf_log, D.grf_log, S * B * 12 * 8, cudaMemcpyDeviceToHost, s));
   }

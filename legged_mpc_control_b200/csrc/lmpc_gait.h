@@ -71,4 +71,46 @@ LMPC_HD inline int gait_predict(int gait, int leg, double phase, double gait_spe
   return 1;                                  // :293 "should not reach here" -> STANCE
 }
 
+// ---- the contact state machine itself: LeggedContactFSM::reset (:16-36), update (:38-84),
+// common_enter (:214-229), percent_in_state (:269-278); the swing-foot Bezier targets are not part of
+// it.  Kept quirk for quirk (host mirror: legged_mpc_control_b200/gait.py ContactFsm, both checked
+// against the compiled reference): `update` TOGGLES stance/swing at every transition instead of
+// reading the pattern entry; the phase is brought back by 1 only when the pattern index wraps, so it
+// is NOT confined to [0, 1] between transitions (predict_contact_state wraps its own copy).
+struct FsmLeg { double phase, start, end; int index, state; };
+
+LMPC_HD inline void fsm_reset(int gait, int leg, FsmLeg& f) {
+  const GaitLeg t = gait_table(gait, leg);
+  f.phase = 0.0; f.index = 0; f.start = 0.0; f.end = t.sw[0]; f.state = t.state[0];
+}
+LMPC_HD inline double fsm_percent(const FsmLeg& f) {
+  double p = (f.phase - f.start) / (f.end - f.start);  // :270 (0/0 -> NaN falls through both clamps, as in the reference)
+  if (p < 0.0) p = 0.0;
+  else if (p > 1.0) p = 1.0;
+  return p;
+}
+LMPC_HD inline void fsm_enter(const GaitLeg& t, FsmLeg& f) {  // common_enter
+  const int prev = f.index;
+  f.index = (f.index + 1) % t.n;
+  if (f.index < prev) f.phase -= 1.0;
+  f.start = f.phase;
+  f.end = t.sw[f.index];
+}
+// one LeggedContactFSM::update(dt, ., ., foot_force_flag); returns the new contact state (1 = STANCE)
+LMPC_HD inline int fsm_update(int gait, int leg, double gait_speed, double dt, bool force_flag, FsmLeg& f) {
+  const GaitLeg t = gait_table(gait, leg);
+#ifdef __CUDA_ARCH__
+  f.phase = __dadd_rn(f.phase, __dmul_rn(gait_speed, dt));  // :50, unfused like the host build
+#else
+  f.phase += gait_speed * dt;
+#endif
+  if (f.state == 1) {
+    if (f.phase >= f.end) { fsm_enter(t, f); f.state = 0; }  // :53-58
+  } else {
+    const double pct = fsm_percent(f);
+    if ((pct > 0.9 && force_flag) || pct >= 1.0) { f.state = 1; fsm_enter(t, f); }  // :59-71
+  }
+  return f.state;
+}
+
 }  // namespace lmpc

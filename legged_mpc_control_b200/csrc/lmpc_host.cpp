@@ -82,19 +82,33 @@ extern "C" int64_t lmpc_abi_sizeof(int32_t which, int32_t field) {
                                  OFF(lmpc_batch_out, reserved0)};
   static const int64_t rst[] = {OFF(lmpc_rollout_state, x), OFF(lmpc_rollout_state, foot_world), OFF(lmpc_rollout_state, phase),
                                 OFF(lmpc_rollout_state, gait), OFF(lmpc_rollout_state, gait_speed), OFF(lmpc_rollout_state, cmd),
-                                OFF(lmpc_rollout_state, on_device), OFF(lmpc_rollout_state, reserved0)};
+                                OFF(lmpc_rollout_state, on_device), OFF(lmpc_rollout_state, reserved0),
+                                OFF(lmpc_rollout_state, fsm_state), OFF(lmpc_rollout_state, fsm_index), OFF(lmpc_rollout_state, fsm_start),
+                                OFF(lmpc_rollout_state, fsm_end)};
   static const int64_t rcfg[] = {OFF(lmpc_rollout_cfg, steps), OFF(lmpc_rollout_cfg, warm_start), OFF(lmpc_rollout_cfg, default_foot_pos_rel),
                                  OFF(lmpc_rollout_cfg, foot_delta_x_limit), OFF(lmpc_rollout_cfg, foot_delta_y_limit), OFF(lmpc_rollout_cfg, ground_z)};
   static const int64_t rres[] = {OFF(lmpc_rollout_result, grf), OFF(lmpc_rollout_result, x_log), OFF(lmpc_rollout_result, grf_log),
                                  OFF(lmpc_rollout_result, solves), OFF(lmpc_rollout_result, factorizations), OFF(lmpc_rollout_result, polish_rounds),
                                  OFF(lmpc_rollout_result, not_converged), OFF(lmpc_rollout_result, warm_hits), OFF(lmpc_rollout_result, flops_executed),
                                  OFF(lmpc_rollout_result, mean_n_eff), OFF(lmpc_rollout_result, device_ms), OFF(lmpc_rollout_result, reserved0)};
+  static const int64_t fsm[] = {OFF(lmpc_fsm_io, gait_phase), OFF(lmpc_fsm_io, fsm_state), OFF(lmpc_fsm_io, fsm_index), OFF(lmpc_fsm_io, fsm_start),
+                                OFF(lmpc_fsm_io, fsm_end), OFF(lmpc_fsm_io, gait), OFF(lmpc_fsm_io, gait_speed), OFF(lmpc_fsm_io, foot_contact_flag),
+                                OFF(lmpc_fsm_io, plan_contacts), OFF(lmpc_fsm_io, contact_table), OFF(lmpc_fsm_io, on_device), OFF(lmpc_fsm_io, reserved0)};
+  static const int64_t leg[] = {OFF(lmpc_leg_io, joint_pos), OFF(lmpc_leg_io, joint_vel), OFF(lmpc_leg_io, rot), OFF(lmpc_leg_io, root_pos),
+                                OFF(lmpc_leg_io, root_lin_vel), OFF(lmpc_leg_io, imu_ang_vel), OFF(lmpc_leg_io, grf), OFF(lmpc_leg_io, foot_pos_target_world),
+                                OFF(lmpc_leg_io, foot_vel_target_world), OFF(lmpc_leg_io, movement_mode), OFF(lmpc_leg_io, foot_pos_rel), OFF(lmpc_leg_io, j_foot),
+                                OFF(lmpc_leg_io, foot_vel_rel), OFF(lmpc_leg_io, foot_pos_abs), OFF(lmpc_leg_io, foot_vel_abs), OFF(lmpc_leg_io, foot_pos_world),
+                                OFF(lmpc_leg_io, foot_vel_world), OFF(lmpc_leg_io, joint_tau_tgt), OFF(lmpc_leg_io, joint_ang_tgt),
+                                OFF(lmpc_leg_io, prev_joint_ang_tgt), OFF(lmpc_leg_io, joint_vel_tgt), OFF(lmpc_leg_io, on_device), OFF(lmpc_leg_io, reserved0)};
+  static const int64_t geo[] = {OFF(lmpc_leg_geometry, rho_fix), OFF(lmpc_leg_geometry, rho_opt)};
 #undef OFF
   static const struct { const int64_t* off; int n; int64_t size; } tab[] = {
       {params, (int)(sizeof(params) / 8), (int64_t)sizeof(lmpc_params)},         {bin, (int)(sizeof(bin) / 8), (int64_t)sizeof(lmpc_batch_in)},
       {bout, (int)(sizeof(bout) / 8), (int64_t)sizeof(lmpc_batch_out)},          {rst, (int)(sizeof(rst) / 8), (int64_t)sizeof(lmpc_rollout_state)},
-      {rcfg, (int)(sizeof(rcfg) / 8), (int64_t)sizeof(lmpc_rollout_cfg)},        {rres, (int)(sizeof(rres) / 8), (int64_t)sizeof(lmpc_rollout_result)}};
-  if (which < 0 || which >= 6) return -1;
+      {rcfg, (int)(sizeof(rcfg) / 8), (int64_t)sizeof(lmpc_rollout_cfg)},        {rres, (int)(sizeof(rres) / 8), (int64_t)sizeof(lmpc_rollout_result)},
+      {fsm, (int)(sizeof(fsm) / 8), (int64_t)sizeof(lmpc_fsm_io)},               {leg, (int)(sizeof(leg) / 8), (int64_t)sizeof(lmpc_leg_io)},
+      {geo, (int)(sizeof(geo) / 8), (int64_t)sizeof(lmpc_leg_geometry)}};
+  if (which < 0 || which >= 9) return -1;
   if (field < 0) return tab[which].size;
   return field < tab[which].n ? tab[which].off[field] : -1;
 }

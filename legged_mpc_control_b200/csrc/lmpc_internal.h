@@ -74,3 +74,41 @@ lmpc_status launch_tile36(const LaunchCtx& c, const KBatch& kb, DevBuf* ws, cons
 lmpc_status launch_tile48(const LaunchCtx& c, const KBatch& kb, DevBuf* ws, const int* order, const int* count, int* work, int nw);
 
 }  // namespace lmpc
+
+// ---- the engine object behind the C ABI (one per GPU), shared by lmpc_api.cu and lmpc_aux.cu
+// Experiment knobs, read ONCE per handle at lmpc_create (never on the solve path).
+struct Tuning {
+  int tile_nw = 0;        // LMPC_TILE_NW: warps per QP of tile classes 1/2 (0 = measured default)
+  bool debug_stats = false;  // LMPC_DEBUG_STATS: print per-solve counters to stderr
+};
+
+struct lmpc_handle {
+  lmpc_params params;
+  lmpc::KParams kp;
+  int device = 0;
+  int max_batch = 0;
+  int num_sms = 0;
+  int smem_optin = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  // device staging for host-pointer calls
+  lmpc::DevBuf d_x0, d_rot, d_foot, d_cmd, d_contact, d_q, d_r, d_mu, d_fz, d_mass, d_inertia;
+  lmpc::DevBuf d_grf, d_status, d_iters, d_active, d_U;
+  lmpc::DevBuf d_stats, d_counter, d_ws, d_wsA, d_wsT1, d_wsT2, d_wsT3, d_order, d_warm;
+  bool warm_enabled = false;
+  int warm_shift = 1;
+  // small-batch host path: one packed H2D and one packed D2H (a single robot's tick is latency-bound)
+  lmpc::DevBuf d_pin, d_pout;
+  unsigned char* h_pin = nullptr;
+  unsigned char* h_pout = nullptr;
+  // closed-loop rollout state (lmpc_rollout)
+  lmpc::DevBuf d_rx, d_rfw, d_rph, d_rgait, d_rspeed, d_rtot, d_xlog, d_glog, d_rfsm;
+  cudaEvent_t ev_r0 = nullptr, ev_r1 = nullptr;
+  Tuning tune;
+  lmpc::KStats last_stats;
+  float last_ms = 0.f;
+  int64_t launches = 0;
+  bool pending = false;
+  cudaStream_t pending_stream = nullptr;
+};
+

@@ -26,6 +26,8 @@ struct RolloutDev {
   // solver output read by the step kernel
   const double* grf;
   double* x_log; double* grf_log;  // optional [steps][B][12]
+  // optional contact state machine (LeggedContactFSM::update): all four or none, [B][4]
+  int* fsm_state; int* fsm_index; double* fsm_start; double* fsm_end;
   int B;
 };
 
@@ -69,6 +71,7 @@ __global__ void rollout_prepare_kernel(const __grid_constant__ KParams P, const 
   for (int leg = 0; leg < 4; ++leg) {
     const double ph = D.phase[4 * p + leg];
     for (int k = 0; k < H; ++k) ct[4 * k + leg] = (uint8_t)gait_predict(gait, leg, ph, speed, __dmul_rn((double)k, P.dt));
+    if (D.fsm_state) ct[leg] = (uint8_t)D.fsm_state[4 * p + leg];  // row 0 = plan_contacts = the FSM's own state (ConvexMpc.cpp:101-104)
     double* fw = D.foot_world + 12 * p + 3 * leg;
     if (!ct[leg]) {  // swing: the foot tracks its foothold target (lands where the target is at touchdown)
       const double rx = C.foot_rel[3 * leg], ry = C.foot_rel[3 * leg + 1];
@@ -151,7 +154,13 @@ __global__ void rollout_step_kernel(const __grid_constant__ KParams P, const __g
 #pragma unroll
   for (int k = 0; k < 12; ++k) D.x[12 * p + k] = x[k];
   const double speed = D.gait_speed[p];
-  for (int leg = 0; leg < 4; ++leg) {
+  for (int leg = 0; leg < 4 && D.fsm_state; ++leg) {  // the reference's state machine (LeggedContactFSM.cpp:38-84); no contact sensing in this plant
+    const size_t k = 4 * p + leg;
+    FsmLeg f = {D.phase[k], D.fsm_start[k], D.fsm_end[k], D.fsm_index[k], D.fsm_state[k]};
+    fsm_update(D.gait[p], leg, speed, dt, false, f);
+    D.phase[k] = f.phase; D.fsm_start[k] = f.start; D.fsm_end[k] = f.end; D.fsm_index[k] = f.index; D.fsm_state[k] = f.state;
+  }
+  for (int leg = 0; leg < 4 && !D.fsm_state; ++leg) {  // stateless variant: wrapped phase only
     double ph = __dadd_rn(D.phase[4 * p + leg], __dmul_rn(speed, dt));  // LeggedContactFSM.cpp:50 (unfused)
     if (ph > 1.0 && ph <= 4503599627370496.0) ph -= ceil(ph) - 1.0;  // == `while (ph > 1) ph -= 1` bit for bit (lmpc_gait.h), O(1)
     D.phase[4 * p + leg] = ph;

@@ -129,13 +129,16 @@ class ConvexMpcEngine:
         out = {}
         if on_device:
             B = int(state["batch"])
-            for k in ("x", "foot_world", "phase", "gait", "gait_speed", "cmd"):
-                setattr(st, k, state[k])
+            for k in ("x", "foot_world", "phase", "gait", "gait_speed", "cmd", "fsm_state", "fsm_index", "fsm_start", "fsm_end"):
+                if k in state:
+                    setattr(st, k, state[k])
             st.on_device = 1
             res.grf, res.x_log, res.grf_log = state.get("grf"), state.get("x_log"), state.get("grf_log")
         else:
             spec = (("x", np.float64, 12), ("foot_world", np.float64, 12), ("phase", np.float64, 4), ("gait", np.int32, 1),
                     ("gait_speed", np.float64, 1), ("cmd", np.float64, 9))
+            if "fsm_state" in state:  # the reference's contact state machine instead of the stateless phase wrap
+                spec = spec + (("fsm_state", np.int32, 4), ("fsm_index", np.int32, 4), ("fsm_start", np.float64, 4), ("fsm_end", np.float64, 4))
             B = np.asarray(state["x"]).size // 12
             for k, dt, per in spec:
                 a = state[k]
@@ -156,6 +159,86 @@ class ConvexMpcEngine:
                    not_converged=res.not_converged, warm_hits=res.warm_hits, flops_executed=res.flops_executed,
                    mean_n_eff=res.mean_n_eff, device_ms=res.device_ms)
         return out
+
+    # -- batched LeggedContactFSM (reset / update) on the device; numpy arrays updated in place
+    def _fsm_io(self, fsm: dict, foot_contact_flag=None, want_table=False):
+        B = np.asarray(fsm["gait"]).size
+        io = abi.LmpcFsmIo()
+        spec = (("gait_phase", np.float64, 4), ("fsm_state", np.int32, 4), ("fsm_index", np.int32, 4), ("fsm_start", np.float64, 4),
+                ("fsm_end", np.float64, 4), ("gait", np.int32, 1), ("gait_speed", np.float64, 1))
+        for k, dt, per in spec:
+            a = fsm[k]
+            if not (isinstance(a, np.ndarray) and a.dtype == dt and a.flags.c_contiguous and a.size == B * per):
+                raise ValueError(f"fsm['{k}'] must be a C-contiguous {np.dtype(dt).name} array of {B}x{per}")
+            setattr(io, k, a.ctypes.data)
+        keep = []
+        if foot_contact_flag is not None:
+            f = np.ascontiguousarray(foot_contact_flag, np.float64).reshape(B, 4)
+            keep.append(f)
+            io.foot_contact_flag = f.ctypes.data
+        out = {"plan_contacts": np.zeros((B, 4), np.uint8)}
+        io.plan_contacts = out["plan_contacts"].ctypes.data
+        if want_table:
+            out["contact"] = np.zeros((B, self.params.horizon, 4), np.uint8)
+            io.contact_table = out["contact"].ctypes.data
+        return io, B, out, keep
+
+    def fsm_reset(self, fsm: dict) -> dict:
+        io, B, out, keep = self._fsm_io(fsm)
+        st = self._L.lmpc_fsm_reset(self._h, B, C.byref(io))
+        if st != abi.OK:
+            raise LmpcError(st, _lib.last_error())
+        return out
+
+    def fsm_update(self, fsm: dict, dt: float, foot_contact_flag=None, want_table: bool = False) -> dict:
+        """One LeggedContactFSM::update(dt, ., ., flag) for every robot-leg; returns plan_contacts [B,4] (+ the
+        solver's contact table [B,H,4] with want_table)."""
+        io, B, out, keep = self._fsm_io(fsm, foot_contact_flag, want_table)
+        st = self._L.lmpc_fsm_update(self._h, B, float(dt), C.byref(io))
+        if st != abi.OK:
+            raise LmpcError(st, _lib.last_error())
+        return out
+
+    # -- SURVEY §8f-3: batched leg kinematics and GRF -> joint command map
+    @staticmethod
+    def a1_geometry() -> abi.LmpcLegGeometry:
+        g = abi.LmpcLegGeometry()
+        _lib.lib().lmpc_leg_geometry_a1(C.byref(g))
+        return g
+
+    def _leg_call(self, fn, arrays: dict, outputs, geometry=None):
+        B = np.asarray(arrays["joint_pos"]).size // 12
+        io = abi.LmpcLegIo()
+        keep = []
+        per = {"joint_pos": 12, "joint_vel": 12, "rot": 9, "root_pos": 3, "root_lin_vel": 3, "imu_ang_vel": 3, "grf": 12,
+               "foot_pos_target_world": 12, "foot_vel_target_world": 12, "movement_mode": 1}
+        for k, n in per.items():
+            if k in arrays and arrays[k] is not None:
+                a = np.ascontiguousarray(arrays[k], np.float64).reshape(B, n)
+                keep.append(a)
+                setattr(io, k, a.ctypes.data)
+        out = {}
+        for k, n in outputs:
+            out[k] = np.array(arrays[k], np.float64).reshape(B, n).copy() if k in arrays else np.zeros((B, n))
+            setattr(io, k, out[k].ctypes.data)
+        g = geometry if geometry is not None else self.a1_geometry()
+        st = fn(self._h, B, C.byref(g), C.byref(io))
+        if st != abi.OK:
+            raise LmpcError(st, _lib.last_error())
+        return out
+
+    def leg_kinematics(self, arrays: dict, geometry=None) -> dict:
+        """BaseInterface.cpp:280-300 for B robots: fk, Jacobian blocks, foot position / velocity in the body,
+        body-aligned ('abs') and world frames."""
+        outs = (("foot_pos_rel", 12), ("j_foot", 36), ("foot_vel_rel", 12), ("foot_pos_abs", 12), ("foot_vel_abs", 12),
+                ("foot_pos_world", 12), ("foot_vel_world", 12))
+        return self._leg_call(self._L.lmpc_leg_kinematics, arrays, outs, geometry)
+
+    def tau_ctrl(self, arrays: dict, geometry=None) -> dict:
+        """BaseInterface::tau_ctrl_update (BaseInterface.cpp:451-500) for B robots: joint torques -J'R'f and the
+        joint angle / velocity targets.  arrays['joint_ang_tgt'] (optional) is the previous target."""
+        outs = (("joint_tau_tgt", 12), ("joint_ang_tgt", 12), ("prev_joint_ang_tgt", 12), ("joint_vel_tgt", 12))
+        return self._leg_call(self._L.lmpc_tau_ctrl, arrays, outs, geometry)
 
     @property
     def launch_count(self) -> int:

@@ -21,6 +21,8 @@ def prepare(params, state, foot_rel, ground_z=0.0, dlim=(0.8, 0.8)):
     B = x.shape[0]
     cmd = state["cmd"]
     contact = gaitmod.contact_table(H, dt, state["gait"], state["phase"], state["gait_speed"])  # [B][H][4]
+    if "fsm_state" in state:  # row 0 = plan_contacts = the state machine's own state (ConvexMpc.cpp:101-104)
+        contact[:, 0, :] = state["fsm_state"]
     cy, sy = np.cos(x[:, 2]), np.sin(x[:, 2])
     vdx = cy * cmd[:, 3] - sy * cmd[:, 4]
     vdy = sy * cmd[:, 3] + cy * cmd[:, 4]
@@ -62,10 +64,20 @@ def rollout(params, state, steps, foot_rel, ground_z=0.0, grf_override=None):
         for i in range(B):
             Ad, Bd, cd = ob.step_matrices(params, batch["rot"][i], batch["foot_pos_abs"][i], state["x"][i, 2])
             state["x"][i] = Ad @ state["x"][i] + Bd @ grf[i] + cd
-        ph = state["phase"] + (state["gait_speed"] * params.dt)[:, None]
-        while (ph > 1.0).any():
-            ph[ph > 1.0] -= 1.0
-        state["phase"][:] = ph
+        if "fsm_state" in state:  # LeggedContactFSM::update per robot-leg (no contact sensing in this plant)
+            for i in range(B):
+                for leg in range(4):
+                    f = gaitmod.ContactFsm(int(state["gait"][i]), leg, float(state["gait_speed"][i]))
+                    f.phase, f.index, f.state = float(state["phase"][i, leg]), int(state["fsm_index"][i, leg]), int(state["fsm_state"][i, leg])
+                    f.start, f.end = float(state["fsm_start"][i, leg]), float(state["fsm_end"][i, leg])
+                    f.update(params.dt, False)
+                    state["phase"][i, leg], state["fsm_index"][i, leg], state["fsm_state"][i, leg] = f.phase, f.index, f.state
+                    state["fsm_start"][i, leg], state["fsm_end"][i, leg] = f.start, f.end
+        else:
+            ph = state["phase"] + (state["gait_speed"] * params.dt)[:, None]
+            while (ph > 1.0).any():
+                ph[ph > 1.0] -= 1.0
+            state["phase"][:] = ph
         x_log[t] = state["x"]
         g_log[t] = grf
     return x_log, g_log

@@ -204,13 +204,14 @@ def test_ctypes_mirror_matches_library_layout(lmpc_lib):
     """sizeof and every offsetof of the ctypes structs in abi.py against what the built library
     reports for include/lmpc.h (lmpc_abi_sizeof): a drifted field would silently shift pointers."""
     import ctypes as C
-    structs = [abi.LmpcParams, abi.LmpcBatchIn, abi.LmpcBatchOut, abi.LmpcRolloutState, abi.LmpcRolloutCfg, abi.LmpcRolloutResult]
+    structs = [abi.LmpcParams, abi.LmpcBatchIn, abi.LmpcBatchOut, abi.LmpcRolloutState, abi.LmpcRolloutCfg, abi.LmpcRolloutResult,
+               abi.LmpcFsmIo, abi.LmpcLegIo, abi.LmpcLegGeometry]
     for which, S in enumerate(structs):
         assert lmpc_lib.lmpc_abi_sizeof(which, -1) == C.sizeof(S), S.__name__
         for i, (name, *_rest) in enumerate(S._fields_):
             assert lmpc_lib.lmpc_abi_sizeof(which, i) == getattr(S, name).offset, (S.__name__, name)
         assert lmpc_lib.lmpc_abi_sizeof(which, len(S._fields_)) == -1  # no field the mirror does not know about
-    assert lmpc_lib.lmpc_abi_sizeof(6, -1) == -1
+    assert lmpc_lib.lmpc_abi_sizeof(9, -1) == -1
 
 
 def test_gait_predict_never_hangs():
