@@ -101,6 +101,8 @@ static void fill_kparams(const lmpc_params& p, KParams* k) {
   if (const char* e = getenv("LMPC_DUAL_REL")) k->dual_rel = atof(e);
   k->try_interior = p.solver == LMPC_SOLVER_ACTIVE_SET ? 1 : 0;
   if (const char* e = getenv("LMPC_TRY_INTERIOR")) k->try_interior = atoi(e);
+  k->tma_prefetch = 0;
+  if (const char* e = getenv("LMPC_TMA_PREFETCH")) k->tma_prefetch = atoi(e);
   for (int i = 0; i < 9; ++i) k->inertia[i] = p.inertia[i];
   for (int i = 0; i < 12; ++i) { k->q[i] = p.q[i]; k->r[i] = p.r[i]; }
 }

@@ -27,6 +27,51 @@ __global__ void __maxnreg__(LMPC_WARP_MAXNREG) solve_warp_kernel(const __grid_co
   const int lane = threadIdx.x;
   const int total = *count;
   WarpStats ws;
+  if (P.tma_prefetch) {
+    // A/B experiment (north_star: "prediction matrices staged in shared memory via TMA"): the persistent
+    // loop runs one work item AHEAD — while problem w solves, lane 0 has already claimed w_next and a
+    // 1-D bulk copy (cp.async.bulk + mbarrier complete_tx) brings its x0 and foot_pos_abs records (96 B
+    // each, 16-byte aligned; rot/cmd records are 72 B and contact 4H B, not bulk-copyable without
+    // over-fetch) into a double-buffered staging area behind the plan.  Measured: see DESIGN.md §4.
+    __shared__ __align__(16) double stage[2][24];
+    __shared__ __align__(8) unsigned long long bar[2];
+    const unsigned bar0 = (unsigned)__cvta_generic_to_shared(&bar[0]), bar1 = (unsigned)__cvta_generic_to_shared(&bar[1]);
+    if (lane == 0) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0));
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar1));
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+    auto claim = [&]() { int w = 0; if (lane == 0) w = atomicAdd(work_counter, 1); return __shfl_sync(0xffffffffu, w, 0); };
+    auto prefetch = [&](int w, int slot) {  // lane 0 only
+      const unsigned b = slot ? bar1 : bar0;
+      const unsigned dst = (unsigned)__cvta_generic_to_shared(&stage[slot][0]);
+      const size_t pi = (size_t)Bt.order[w];
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], 192;" ::"r"(b) : "memory");
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], 96, [%2];" ::"r"(dst),
+                   "l"(Bt.x0 + 12 * pi), "r"(b) : "memory");
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], 96, [%2];" ::"r"(dst + 96),
+                   "l"(Bt.foot + 12 * pi), "r"(b) : "memory");
+    };
+    int w = claim(), slot = 0;
+    unsigned phase[2] = {0u, 0u};
+    if (w < total && lane == 0) prefetch(w, 0);
+    while (w < total) {
+      const int w_next = claim();
+      if (w_next < total && lane == 0) prefetch(w_next, slot ^ 1);
+      const unsigned b = slot ? bar1 : bar0;
+      unsigned done = 0;
+      while (!done)
+        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                     : "=r"(done) : "r"(b), "r"(phase[slot]) : "memory");
+      phase[slot] ^= 1u;
+      solve_one_warp(P, Bt, ws, pl, smem, Hg, Bt.order[w], &stage[slot][0], &stage[slot][12]);
+      w = w_next;
+      slot ^= 1;
+    }
+    flush_warp_stats(ws, stats);
+    return;
+  }
   for (;;) {
     int w = 0;
     if (lane == 0) w = atomicAdd(work_counter, 1);

@@ -20,6 +20,7 @@ struct KParams {
   double dual_rel;  // multiplier sign tolerance of the exact polish, relative to the gradient scale
   int sigma_pow;    // exponent of the Mehrotra centering rule (3)
   int try_interior; // experiment: cold problems first try the polish from all-interior faces
+  int tma_prefetch; // experiment: stage the NEXT problem's x0/foot records by TMA bulk copy while this one solves
   double inertia[9];
   double q[12];
   double r[12];

@@ -116,8 +116,11 @@ __device__ __forceinline__ void pair_from_index(int pr, int& b1, int& b2) {
   b2 = pr - (b1 * (b1 + 1)) / 2;
 }
 
+// x0_s / foot_s: optional copies of this problem's x0[12] / foot_pos_abs[12] records already staged in
+// shared memory (TMA bulk prefetch, lmpc_k_warp.cu); nullptr -> read them from global memory.
 static __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpStats& ws, const WarpPlan& pl,
-                               unsigned char* smem, double* Hg, int pi) {
+                               unsigned char* smem, double* Hg, int pi, const double* x0_s = nullptr,
+                               const double* foot_s = nullptr) {
   const int lane = threadIdx.x & 31;
   const int H = P.H;
   double* sd = reinterpret_cast<double*>(smem);
@@ -145,9 +148,9 @@ static __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpSt
 
   const double dt = P.dt, dt2 = P.dt * P.dt, theta = P.zoh ? 0.5 : 0.0;
   const size_t p64 = (size_t)pi;
-  const double* x0 = Bt.x0 + 12 * p64;
+  const double* x0 = x0_s ? x0_s : Bt.x0 + 12 * p64;
   const double* rot = Bt.rot + 9 * p64;
-  const double* foot = Bt.foot + 12 * p64;
+  const double* foot = foot_s ? foot_s : Bt.foot + 12 * p64;
   const double* cmd = Bt.cmd + 9 * p64;
   const uint8_t* contact = Bt.contact + (size_t)(4 * H) * p64;
 
