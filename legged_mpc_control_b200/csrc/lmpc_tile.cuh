@@ -198,16 +198,31 @@ __device__ __forceinline__ void gm_solve_impl(const double* Ls, double* x, const
   // forward: y_J = inv(L_JJ) (b_J - sum_{K<J} L_JK y_K)
 #pragma unroll 1
   for (int J = 0; J < nte; ++J) {  // blocks beyond the problem's own tile count are identity with zero right-hand sides
-    double p0 = 0.0, p1 = 0.0;
+    // NT > 24 (factor in the CTA's L2 slot): eight independent accumulators, i.e. four 400-cycle loads in
+    // flight per dependent chain (all-gait H=30 batch +17 %); the shared-memory classes keep the two-chain
+    // loop, which measured faster there (C3 624k vs 554k, trot H=30 139k vs 127k)
+    double pa[4] = {0.0, 0.0, 0.0, 0.0}, pb[4] = {0.0, 0.0, 0.0, 0.0};
     const double2* p = Lf + 32 * J;  // tile (J, 0); tile (J, K+1) is NT - K - 1 tiles further
+    int K = 0;
+    for (; NT > 24 && K + 4 <= J; K += 4) {  // (the factor of these classes lives in L2: four loads in flight per chain)
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const double2 l = *p;
+        const double2 y = xt[4 * (K + u)];
+        pa[u] = fma(l.x, y.x, pa[u]);
+        pb[u] = fma(l.y, y.y, pb[u]);
+        p += 32 * (NT - (K + u) - 1);
+      }
+    }
 #pragma unroll 4
-    for (int K = 0; K < J; ++K) {
+    for (; K < J; ++K) {
       const double2 l = *p;
       const double2 y = xt[4 * K];
-      p0 = fma(l.x, y.x, p0);
-      p1 = fma(l.y, y.y, p1);
+      pa[0] = fma(l.x, y.x, pa[0]);
+      pb[0] = fma(l.y, y.y, pb[0]);
       p += 32 * (NT - K - 1);
     }
+    const double p0 = (pa[0] + pa[1]) + (pa[2] + pa[3]), p1 = (pb[0] + pb[1]) + (pb[2] + pb[3]);
     double2 r = xt[4 * J];
     if (J > 0) {
       const double2 s = quad_reduce_t(p0 + p1);
@@ -220,13 +235,23 @@ __device__ __forceinline__ void gm_solve_impl(const double* Ls, double* x, const
 #pragma unroll 1
   for (int J = nte - 1; J >= 0; --J) {
     const double* ct = Ls + 64 * G::lcol(J) + 16 * t + g;  // transposed reads of column J: tile i at ct[64 i], ct[64 i + 8]
-    double p0 = 0.0, p1 = 0.0;
-#pragma unroll 4
-    for (int i = 1; i < nte - J; ++i) {
-      const double2 xi = xt[4 * (J + i)];
-      p0 = fma(ct[64 * i], xi.x, p0);
-      p1 = fma(ct[64 * i + 8], xi.y, p1);
+    double pa[4] = {0.0, 0.0, 0.0, 0.0}, pb[4] = {0.0, 0.0, 0.0, 0.0};
+    int i = 1;
+    for (; NT > 24 && i + 4 <= nte - J; i += 4) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const double2 xi = xt[4 * (J + i + u)];
+        pa[u] = fma(ct[64 * (i + u)], xi.x, pa[u]);
+        pb[u] = fma(ct[64 * (i + u) + 8], xi.y, pb[u]);
+      }
     }
+#pragma unroll 4
+    for (; i < nte - J; ++i) {
+      const double2 xi = xt[4 * (J + i)];
+      pa[0] = fma(ct[64 * i], xi.x, pa[0]);
+      pb[0] = fma(ct[64 * i + 8], xi.y, pb[0]);
+    }
+    const double p0 = (pa[0] + pa[1]) + (pa[2] + pa[3]), p1 = (pb[0] + pb[1]) + (pb[2] + pb[3]);
     double2 r = xt[4 * J];
     if (J < nte - 1) {
       const double2 s = quad_reduce_t(p0 + p1);
