@@ -267,6 +267,104 @@ static __device__ __noinline__ void gm_solve(const double* Ls, double* x, int nt
   else gm_solve_impl<NT>(Ls, x, nte);
 }
 
+// ---- the same solve spread over the NW warps of a CTA: blocked substitution with BS tile rows per
+// block.  Per block, warp 0 solves the BS x BS triangle (short chains), then all warps subtract the
+// block's contribution from the remaining rows (independent rows: one per warp at a time), two CTA
+// barriers per block.  Every warp of the CTA must call it.  x is in shared memory, t-layout.
+template <int NT, int NW>
+__device__ __forceinline__ void gm_solve_mw_impl(const double* Ls, double* x, const int nte, const int w) {
+  using G = TileGeom<NT>;
+  constexpr int BS = 4;
+  const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const double2* Lf = reinterpret_cast<const double2*>(Ls) + lane;
+  double2* xt = reinterpret_cast<double2*>(x) + t;
+  // forward
+  for (int d0 = 0; d0 < nte; d0 += BS) {
+    const int d1 = d0 + BS < nte ? d0 + BS : nte;
+    if (w == 0) {
+      for (int J = d0; J < d1; ++J) {
+        double p0 = 0.0, p1 = 0.0;
+        for (int K = d0; K < J; ++K) {
+          const double2 l = Lf[32 * (G::lcol(K) + J - K)];
+          const double2 y = xt[4 * K];
+          p0 = fma(l.x, y.x, p0);
+          p1 = fma(l.y, y.y, p1);
+        }
+        double2 r = xt[4 * J];
+        if (J > d0) {
+          const double2 s = quad_reduce_t(p0 + p1);
+          r.x -= s.x; r.y -= s.y;
+        }
+        const double2 li = Lf[32 * G::lcol(J)];
+        xt[4 * J] = quad_reduce_t(fma(li.x, r.x, li.y * r.y));
+      }
+    }
+    __syncthreads();
+    for (int I = d1 + w; I < nte; I += NW) {  // x_I -= sum_{K in block} L_IK y_K
+      double p0 = 0.0, p1 = 0.0;
+#pragma unroll
+      for (int u = 0; u < BS; ++u) {
+        const int K = d0 + u;
+        if (K < d1) {
+          const double2 l = Lf[32 * (G::lcol(K) + I - K)];
+          const double2 y = xt[4 * K];
+          p0 = fma(l.x, y.x, p0);
+          p1 = fma(l.y, y.y, p1);
+        }
+      }
+      const double2 s = quad_reduce_t(p0 + p1);
+      double2 r = xt[4 * I];
+      r.x -= s.x; r.y -= s.y;
+      xt[4 * I] = r;
+    }
+    __syncthreads();
+  }
+  // backward: blocks from the bottom
+  for (int d1 = nte; d1 > 0; d1 -= BS) {
+    const int d0 = d1 - BS > 0 ? d1 - BS : 0;
+    if (w == 0) {
+      for (int J = d1 - 1; J >= d0; --J) {
+        const double* ct = Ls + 64 * G::lcol(J) + 16 * t + g;  // transposed reads of column J: tile (J + i, J) at ct[64 i], ct[64 i + 8]
+        double p0 = 0.0, p1 = 0.0;
+        for (int I = J + 1; I < d1; ++I) {
+          const double2 xi = xt[4 * I];
+          p0 = fma(ct[64 * (I - J)], xi.x, p0);
+          p1 = fma(ct[64 * (I - J) + 8], xi.y, p1);
+        }
+        double2 r = xt[4 * J];
+        if (J < d1 - 1) {
+          const double2 s = quad_reduce_t(p0 + p1);
+          r.x -= s.x; r.y -= s.y;
+        }
+        xt[4 * J] = quad_reduce_t(fma(ct[0], r.x, ct[8] * r.y));
+      }
+    }
+    __syncthreads();
+    for (int J = w; J < d0; J += NW) {  // y_J -= sum_{I in block} L_IJ' x_I
+      const double* ct = Ls + 64 * G::lcol(J) + 16 * t + g;
+      double p0 = 0.0, p1 = 0.0;
+#pragma unroll
+      for (int u = 0; u < BS; ++u) {
+        const int I = d0 + u;
+        if (I < d1) {
+          const double2 xi = xt[4 * I];
+          p0 = fma(ct[64 * (I - J)], xi.x, p0);
+          p1 = fma(ct[64 * (I - J) + 8], xi.y, p1);
+        }
+      }
+      const double2 s = quad_reduce_t(p0 + p1);
+      double2 r = xt[4 * J];
+      r.x -= s.x; r.y -= s.y;
+      xt[4 * J] = r;
+    }
+    __syncthreads();
+  }
+}
+template <int NT, int NW>
+static __device__ __noinline__ void gm_solve_mw(const double* Ls, double* x, int nte, int w) {
+  gm_solve_mw_impl<NT, NW>(Ls, x, nte, w);
+}
+
 // y = H x for the full-symmetric workspace (global, L2); x, y (8 NT)-vectors in shared memory.
 // Tile rows I = i0, i0 + di, ...: one warp does them all (i0 = 0, di = 1) or the warps of the CTA
 // take every NW-th row (job 5).

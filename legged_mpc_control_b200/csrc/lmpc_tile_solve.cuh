@@ -214,6 +214,21 @@ __device__ __forceinline__ void tile_symv(const double* Hg, const double* x, dou
   gm_symv<NT>(Hg, x, y, nte, 0, NW);
   __syncthreads();
 }
+// L L' x = b with the substitution blocked over the warps of the CTA (job 6); x in shared memory.
+template <int NT, int NW>
+__device__ __forceinline__ void tile_solve(const double* Ls, double* x, int nte) {
+  // Measured (solves/s, one-warp solve vs blocked over the CTA): NT=15 C3 618k vs 535k, NT=24 trot H=30 139k vs
+  // 137k (shared-memory factor: the barriers cost what the parallel rows save); NT=36/48 all-gait H=30 43.6k vs
+  // 50.6k (factor in L2: four warps keep four times as many 400-cycle loads in flight).  So only the L2 classes.
+  if (NW == 1 || NT <= 24) { gm_solve<NT>(Ls, x, nte); return; }
+  if ((threadIdx.x & 31) == 0) {
+    TileJobArgs* a = tile_job_args();
+    a->y = x; a->nte = nte;
+    *tile_job() = 6;
+  }
+  __syncthreads();
+  gm_solve_mw<NT, NW>(Ls, x, nte, 0);
+}
 // Helper warps (1 .. NW-1) live here until warp 0 posts job 0.
 template <int NT, int NW>
 __device__ __forceinline__ void tile_helper_loop(const KParams& P, const TilePlan& pl, unsigned char* smem, double* Hg) {
@@ -229,7 +244,8 @@ __device__ __forceinline__ void tile_helper_loop(const KParams& P, const TilePla
       const TileJobArgs a = *tile_job_args();
       if (job == 3) tile_hessian_blocks<NT>(P, pl, smem, Hg, a.nb, a.n, a.sc, a.im2, threadIdx.x, 32 * NW);
       else if (job == 4) tile_reduced_matrix<NT>(pl, smem, Hg, a.nb, a.n, a.mu, threadIdx.x, 32 * NW);
-      else gm_symv<NT>(Hg, a.x, a.y, a.nte, w, NW);
+      else if (job == 5) gm_symv<NT>(Hg, a.x, a.y, a.nte, w, NW);
+      else { gm_solve_mw<NT, NW>(tile_ls<NT>(pl, smem, Hg), a.y, a.nte, w); continue; }  // job 6 ends on its own barrier
       __syncthreads();
     }
   }
@@ -551,7 +567,7 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
       }
       __syncwarp();
       if (!tile_factor<NT, NW, true>(Hg, Ls, xb, nte)) { ipm_broken = true; break; }
-      gm_solve<NT>(Ls, dua, nte);
+      tile_solve<NT, NW>(Ls, dua, nte);
       __syncwarp();
       double tau = 0.0;
       for (int b = lane; b < nb; b += 32) {
@@ -596,7 +612,7 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
         }
       }
       __syncwarp();
-      gm_solve<NT>(Ls, du, nte);
+      tile_solve<NT, NW>(Ls, du, nte);
       __syncwarp();
       double tau2 = 0.0;
       for (int b = lane; b < nb; b += 32) {
@@ -709,7 +725,7 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
       }
       __syncwarp();
       if (!tile_factor<NT, NW, false>(Hg, Ls, xb, nte)) break;
-      gm_solve<NT>(Ls, du, nte);
+      tile_solve<NT, NW>(Ls, du, nte);
       for (int i = lane; i < N; i += 32) dua[i] = 0.0;
       __syncwarp();
       for (int b = lane; b < nb; b += 32) {
@@ -773,7 +789,7 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
         du[3 * b + 2] = (apex || top) ? 0.0 : -gzt;
       }
       __syncwarp();
-      gm_solve<NT>(Ls, du, nte);
+      tile_solve<NT, NW>(Ls, du, nte);
       __syncwarp();
       for (int b = lane; b < nb; b += 32) {
         const int sx = face[4 * b], sy = face[4 * b + 1];
