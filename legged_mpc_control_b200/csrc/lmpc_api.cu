@@ -101,6 +101,10 @@ static void fill_kparams(const lmpc_params& p, KParams* k) {
   if (const char* e = getenv("LMPC_DUAL_REL")) k->dual_rel = atof(e);
   k->try_interior = p.solver == LMPC_SOLVER_ACTIVE_SET ? 1 : 0;
   if (const char* e = getenv("LMPC_TRY_INTERIOR")) k->try_interior = atoi(e);
+  k->class0_on_tiles = 0;
+  if (const char* e = getenv("LMPC_CLASS0_TILES")) k->class0_on_tiles = atoi(e);
+  k->warp_occ_cap = 0;
+  if (const char* e = getenv("LMPC_WARP_OCC")) k->warp_occ_cap = atoi(e);
   k->tma_prefetch = 0;
   if (const char* e = getenv("LMPC_TMA_PREFETCH")) k->tma_prefetch = atoi(e);
   for (int i = 0; i < 9; ++i) k->inertia[i] = p.inertia[i];
@@ -201,7 +205,8 @@ static lmpc_status launch_solve(lmpc_handle* h, KBatch kb, cudaStream_t s) {
   h->launches++;
   const lmpc::LaunchCtx c{h->device, &h->kp, dstats, h->num_sms, s, &h->launches};
   const int nmax = 12 * H;  // largest reduced dimension this horizon can produce
-  lmpc_status st = lmpc::launch_warp_class(c, kb, &h->d_wsA, order, cnt + 0, ctr + 0);
+  lmpc_status st = h->kp.class0_on_tiles ? lmpc::launch_tile8(c, kb, &h->d_wsA, order, cnt + 0, ctr + 0, 1)
+                                         : lmpc::launch_warp_class(c, kb, &h->d_wsA, order, cnt + 0, ctr + 0);
   if (st != LMPC_OK) return st;
   if (nmax > lmpc::kWarpNMax) {
     st = lmpc::launch_tile15(c, kb, &h->d_wsT1, order + stride, cnt + 1, ctr + 1, h->tune.tile_nw);

@@ -68,6 +68,7 @@ struct LaunchCtx {
 // own L2-resident workspace, grown on demand.
 lmpc_status launch_warp_class(const LaunchCtx& c, const KBatch& kb, DevBuf* ws, const int* order, const int* count, int* work);
 // nw: warps per QP (1, 2 or 4; 0 = the measured default of the class)
+lmpc_status launch_tile8(const LaunchCtx& c, const KBatch& kb, DevBuf* ws, const int* order, const int* count, int* work, int nw);
 lmpc_status launch_tile15(const LaunchCtx& c, const KBatch& kb, DevBuf* ws, const int* order, const int* count, int* work, int nw);
 lmpc_status launch_tile24(const LaunchCtx& c, const KBatch& kb, DevBuf* ws, const int* order, const int* count, int* work, int nw);
 lmpc_status launch_tile36(const LaunchCtx& c, const KBatch& kb, DevBuf* ws, const int* order, const int* count, int* work, int nw);

@@ -70,7 +70,13 @@ static lmpc_status launch_tile_nw(const LaunchCtx& c, const KBatch& kb, DevBuf* 
 
 // Warps per QP, measured (C3 / reference preset, solves/s): NT=15: 598k / 647k / 519k at 1 / 2 / 4 warps
 // (4 warps cost the third CTA per SM); NT=24: 90k / 106k / 146k (one CTA per SM anyway); NT=36/48: 4.
-#if LMPC_TILE_NT == 15
+#if LMPC_TILE_NT == 8
+// experiment: the rolled tile code at the one-warp size, one warp per QP — an A/B against
+// solve_warp_kernel's straight-line code for the instruction-cache question
+lmpc_status launch_tile8(const LaunchCtx& c, const KBatch& kb, DevBuf* ws, const int* order, const int* count, int* work, int) {
+  return launch_tile_nw<8, 1>(c, kb, ws, order, count, work);
+}
+#elif LMPC_TILE_NT == 15
 lmpc_status launch_tile15(const LaunchCtx& c, const KBatch& kb, DevBuf* ws, const int* order, const int* count, int* work, int nw) {
   if (nw == 0) nw = kb.B <= c.num_sms ? 4 : 2;  // fewer problems than SMs: latency counts, occupancy does not
   if (nw == 1) return launch_tile_nw<15, 1>(c, kb, ws, order, count, work);

@@ -16,7 +16,8 @@ namespace lmpc {
 // One warp per CTA: no block barrier exists in this kernel.  Problems are handed out by an atomic
 // counter; the scaled Hessian of the problem in flight lives in this CTA's 32 KB slot of the
 // L2-resident workspace `gws`.
-__global__ void __maxnreg__(LMPC_WARP_MAXNREG) solve_warp_kernel(const __grid_constant__ KParams P,
+template <int MAXNREG>
+__global__ void __maxnreg__(MAXNREG) solve_warp_kernel_r(const __grid_constant__ KParams P,
                                                         const __grid_constant__ KBatch Bt,
                                                         KStats* stats, double* gws,
                                                         const int* __restrict__ count,
@@ -82,7 +83,12 @@ __global__ void __maxnreg__(LMPC_WARP_MAXNREG) solve_warp_kernel(const __grid_co
   flush_warp_stats(ws, stats);
 }
 
-lmpc_status launch_warp_class(const LaunchCtx& c, const KBatch& kb, DevBuf* ws, const int* order, const int* count, int* work) {
+// Register cap -> resident warps per SM (shared memory allows 10 since the exchange buffers went): 255 -> 8,
+// 224 -> 9, 200 -> 10.  Measured this round on the headline workload: 4.12 / 4.13 / 4.14 M solves/s — a third
+// warp per scheduler adds nothing (the second one already saturates instruction fetch), so 255.
+template <int MAXNREG>
+static lmpc_status launch_warp_r(const LaunchCtx& c, const KBatch& kb, DevBuf* ws, const int* order, const int* count, int* work) {
+  auto solve_warp_kernel = solve_warp_kernel_r<MAXNREG>;
   const WarpPlan wp = make_warp_plan(c.kp->H);
   static int occ_dev[kMaxDevices], bytes_dev[kMaxDevices];  // per device: the attribute lives in the device's context
   int& occ_cached = occ_dev[c.device];
@@ -93,7 +99,9 @@ lmpc_status launch_warp_class(const LaunchCtx& c, const KBatch& kb, DevBuf* ws, 
     occ_bytes = wp.total_bytes;
   }
   if (occ_cached < 1) { set_err("warp solve kernel does not fit on an SM"); return LMPC_ERR_CUDA; }
-  int grid = c.num_sms * occ_cached;
+  int occ = occ_cached;
+  if (c.kp->warp_occ_cap > 0 && occ > c.kp->warp_occ_cap) occ = c.kp->warp_occ_cap;  // experiment: fewer resident warps
+  int grid = c.num_sms * occ;
   if (grid > kb.B) grid = kb.B;
   CK(ws->ensure((size_t)grid * WN * WN * sizeof(double)));
   KBatch k = kb;
@@ -102,6 +110,10 @@ lmpc_status launch_warp_class(const LaunchCtx& c, const KBatch& kb, DevBuf* ws, 
   ++*c.launches;
   CK(cudaGetLastError());
   return LMPC_OK;
+}
+
+lmpc_status launch_warp_class(const LaunchCtx& c, const KBatch& kb, DevBuf* ws, const int* order, const int* count, int* work) {
+  return launch_warp_r<LMPC_WARP_MAXNREG>(c, kb, ws, order, count, work);
 }
 
 }  // namespace lmpc

@@ -20,6 +20,8 @@ struct KParams {
   double dual_rel;  // multiplier sign tolerance of the exact polish, relative to the gradient scale
   int sigma_pow;    // exponent of the Mehrotra centering rule (3)
   int try_interior; // experiment: cold problems first try the polish from all-interior faces
+  int class0_on_tiles; // experiment: run size class 0 on solve_tile_kernel<8,1> (rolled code) instead of solve_warp_kernel
+  int warp_occ_cap; // experiment: cap on resident warps per SM of the one-warp kernel (0 = none)
   int tma_prefetch; // experiment: stage the NEXT problem's x0/foot records by TMA bulk copy while this one solves
   double inertia[9];
   double q[12];

@@ -31,10 +31,14 @@ __host__ __device__ inline WarpPlan make_warp_plan(int H) {
   p.oRD = o; o += WN;
   p.oDUA = o; o += WN;
   p.oDU = o; o += WN;
-  p.oWROW = o; o += 3 * WN;
-  p.oZ = o; o += 112;
+  p.oWROW = o; o += 16;  // active-set words under construction (<= 24 x 32 bits)
+  p.oZ = o;              // (multipliers live in registers)
   p.oPRM = o; o += 32;
-  p.oXB = o; o += 64;
+#ifdef LMPC_DIAG8_SMEM
+  p.oXB = o; o += 64;    // pivot-row exchange of the shared-memory diagonal-tile variant
+#else
+  p.oXB = o;             // wm_diag8_mma needs no exchange buffer
+#endif
   p.n_doubles = o;
   int b = o * 8;
   p.oBLK = b; b += 2 * 24;

@@ -220,10 +220,14 @@ __device__ __forceinline__ double2 wm_diag8_impl(double ax, double ay, double* x
 //   * G' = F D' (2x2 Cholesky inverse of every pivot block, per-lane column pair) and one
 //     identity-DMMA pair transposes G' into the C-layout of G.
 // 16 DMMAs + 12 SHFLs per tile instead of ~400 instructions, and the F chain runs beside the A chain.
+#ifndef LMPC_DIAG8_UNROLL
+#define LMPC_DIAG8_UNROLL 3
+#endif
+constexpr int kDiag8Unroll = LMPC_DIAG8_UNROLL;
 __device__ __forceinline__ double2 wm_diag8_mma(double ax, double ay) {
   const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   double fx = (g == 2 * t) ? 1.0 : 0.0, fy = (g == 2 * t + 1) ? 1.0 : 0.0;
-#pragma unroll
+#pragma unroll kDiag8Unroll
   for (int s = 0; s < 3; ++s) {
     const int src = 9 * s;  // lane (g = 2s, t = s)
     const double a = __shfl_sync(0xffffffffu, ax, src);
