@@ -387,8 +387,8 @@ def run_b200(args):
             "roofline": {
                 "bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
                 "traffic": _ncu_traffic() if _WL == "headline" else None,
-                "traffic_source": "profiles/r01_v15_ncu_full_solve_warp_kernel.csv (bytes per launch; input reads + write-backs of the L2-resident "
-                                  "Hessian workspace, <0.1% of HBM peak: the bound is FP64 latency, not DRAM)",
+                "traffic_source": "profiles/" + NCU_TRAFFIC_FILE + " (bytes per launch; input reads + write-backs of the L2-resident "
+                                  "Hessian workspace, ~0.2% of HBM peak: the bound is FP64 latency / instruction fetch, not DRAM)",
                 "kernel": "lmpc::solve_warp_kernel" if stats["mean_n_eff"] <= 63 else "lmpc::solve_tile_kernel / solve_kernel (by size class)",
                 "kernel_ms": kms,
                 "precision": "fp64", "peak_source": "measured on this GPU by lmpc_microbench_fp64 (MEASURED_PEAKS.json has no FP64 entry)",
@@ -522,10 +522,13 @@ def _parity(p, kept, tout, n):
             "status_counts": np.bincount(got["status"], minlength=4).tolist(), "tolerance": pu.REL_TOL}
 
 
+NCU_TRAFFIC_FILE = "r02_v6_ncu_full_solve_warp_kernel.csv"  # one 65 536-problem launch of the headline workload, `ncu --set full`
+
+
 def _ncu_traffic():
     """dram__bytes_read.sum + dram__bytes_write.sum of one solve_warp_kernel launch of the headline
     workload, from the committed `ncu --set full` capture (bench.py never runs under a profiler)."""
-    path = os.path.join(ROOT, "profiles", "r01_v15_ncu_full_solve_warp_kernel.csv")
+    path = os.path.join(ROOT, "profiles", NCU_TRAFFIC_FILE)
     try:
         tot = 0.0
         for ln in open(path):
