@@ -691,7 +691,7 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
       __syncwarp();
     }
     bool polished = false;
-    for (int round = 0; round < 6; ++round) {
+    for (int round = 0; round < 10; ++round) {
       ++n_polish;
       // p (pinned particular solution) in rd ; hu = H p
       for (int i = lane; i < N; i += 32) rd[i] = 0.0;
@@ -738,34 +738,32 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
       __syncwarp();
       tile_symv<NT, NW>(Hg, dua, hu, nte);
       __syncwarp();
+      // Face repair (face_step, lmpc_blocks.cuh; same rule as solve_one_warp): rounds 0-2 apply every indicated
+      // change at once; from round 3 on, adds while any block is primal infeasible, else the single most
+      // violated multiplier of the whole problem is dropped.  A lane owns the blocks b = lane, lane + 32, ...
       int changed = 0;
-      for (int b = lane; b < nb; b += 32) {
-        int sx = face[4 * b], sy = face[4 * b + 1], top = face[4 * b + 2], apex = face[4 * b + 3];
-        const double gx = hu[3 * b] + gs[3 * b], gy = hu[3 * b + 1] + gs[3 * b + 1], gz = hu[3 * b + 2] + gs[3 * b + 2];
-        const double fx = dua[3 * b], fy = dua[3 * b + 1], fz = dua[3 * b + 2];
-        if (apex) {
-          if (gz < mu * (fabs(gx) + fabs(gy)) - dual_tol) {
-            apex = 0; top = 0;
-            sx = gx > 0 ? -1 : (gx < 0 ? 1 : 0);
-            sy = gy > 0 ? -1 : (gy < 0 ? 1 : 0);
-            changed = 1;
-          }
-        } else {
-          const double gvz = gz + mu * (sx * gx + sy * gy);
-          const bool dropx = sx != 0 && ((sx == -1 ? gx : -gx) < -dual_tol);
-          const bool dropy = sy != 0 && ((sy == -1 ? gy : -gy) < -dual_tol);
-          const bool dropt = top && (-gvz < -dual_tol);
-          int nsx = dropx ? 0 : sx, nsy = dropy ? 0 : sy, ntop = dropt ? 0 : top, napex = 0;
-          if (fz > fzm + feas_tol) ntop = 1;
-          if (fz < -feas_tol) napex = 1;
-          else {
-            if (sx == 0) { if (-fx - mu * fz > feas_tol) nsx = -1; else if (fx - mu * fz > feas_tol) nsx = 1; }
-            if (sy == 0) { if (-fy - mu * fz > feas_tol) nsy = -1; else if (fy - mu * fz > feas_tol) nsy = 1; }
-          }
-          if (nsx != sx || nsy != sy || ntop != top || napex != apex) changed = 1;
-          sx = nsx; sy = nsy; top = ntop; apex = napex;
+      bool any_add = false;
+      double dmax = 0.0;
+      if (round >= 3) {  // first pass: is any block infeasible, and what is the largest multiplier violation
+        bool add = false;
+        double dloc = 0.0;
+        for (int b = lane; b < nb; b += 32) {
+          const FaceStep fs = face_step(face[4 * b], face[4 * b + 1], face[4 * b + 2], face[4 * b + 3], hu[3 * b] + gs[3 * b],
+                                        hu[3 * b + 1] + gs[3 * b + 1], hu[3 * b + 2] + gs[3 * b + 2], dua[3 * b], dua[3 * b + 1],
+                                        dua[3 * b + 2], mu, fzm, dual_tol, feas_tol, false);
+          add = add || fs.add;
+          dloc = fmax(dloc, fs.dscore);
         }
-        face[4 * b] = (signed char)sx; face[4 * b + 1] = (signed char)sy; face[4 * b + 2] = (signed char)top; face[4 * b + 3] = (signed char)apex;
+        any_add = __any_sync(0xffffffffu, add);
+        dmax = wmax(dloc);
+      }
+      for (int b = lane; b < nb; b += 32) {
+        const double gx = hu[3 * b] + gs[3 * b], gy = hu[3 * b + 1] + gs[3 * b + 1];
+        FaceStep fs = face_step(face[4 * b], face[4 * b + 1], face[4 * b + 2], face[4 * b + 3], gx, gy, hu[3 * b + 2] + gs[3 * b + 2],
+                                dua[3 * b], dua[3 * b + 1], dua[3 * b + 2], mu, fzm, dual_tol, feas_tol, round < 3);
+        if (round >= 3 && !any_add && fs.dwhich >= 0 && fs.dscore == dmax) face_single_drop(fs, gx, gy);
+        if (fs.sx != face[4 * b] || fs.sy != face[4 * b + 1] || fs.top != face[4 * b + 2] || fs.apex != face[4 * b + 3]) changed = 1;
+        face[4 * b] = (signed char)fs.sx; face[4 * b + 1] = (signed char)fs.sy; face[4 * b + 2] = (signed char)fs.top; face[4 * b + 3] = (signed char)fs.apex;
       }
       const bool any_changed = __any_sync(0xffffffffu, changed);
       double fsum = 0.0;  // NaN compares false everywhere above: a non-finite solve must never pass as verified

@@ -679,74 +679,26 @@ static __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpSt
       __syncwarp();
       wm_symv(Hg, dua, hu);
       __syncwarp();
-      // Face repair.  Rounds 0-2 apply every indicated change at once (fast, usually 1-2 rounds).
-      // From round 3 on the classical one-change-at-a-time rule takes over so that the iteration
-      // cannot cycle: while any block is primal infeasible only constraints are ADDED; otherwise
-      // only the single most violated multiplier (largest dual violation of the warp) is DROPPED.
+      // Face repair (face_step, lmpc_blocks.cuh): rounds 0-2 apply every indicated change at once; from round 3
+      // on, adds while any block is primal infeasible, else the single most violated multiplier is dropped.
       int changed = 0;
-      int sx = 0, sy = 0, top = 0, apex = 0, nsx = 0, nsy = 0, ntop = 0, napex = 0;
-      bool add = false;
-      double dscore = 0.0;
-      int dwhich = -1;  // 0: x face, 1: y face, 2: top, 3: leave the apex
+      FaceStep fs = {0, 0, 0, 0, false, 0.0, -1};
+      double gxb = 0.0, gyb = 0.0;
       if (lane < nb) {
         const int b = lane;
-        sx = face[4 * b]; sy = face[4 * b + 1]; top = face[4 * b + 2]; apex = face[4 * b + 3];
-        const double gx = hu[3 * b] + gs[3 * b], gy = hu[3 * b + 1] + gs[3 * b + 1], gz = hu[3 * b + 2] + gs[3 * b + 2];
-        const double fx = dua[3 * b], fy = dua[3 * b + 1], fz = dua[3 * b + 2];
-        nsx = sx; nsy = sy; ntop = top; napex = apex;
-        if (apex) {
-          const double v = mu * (fabs(gx) + fabs(gy)) - gz;
-          if (v > dual_tol) { dscore = v; dwhich = 3; }
-        } else {
-          const double gvz = gz + mu * (sx * gx + sy * gy);
-          const double vx = sx != 0 ? -(sx == -1 ? gx : -gx) : 0.0;
-          const double vy = sy != 0 ? -(sy == -1 ? gy : -gy) : 0.0;
-          const double vt = top ? gvz : 0.0;
-          if (vx > dual_tol) { dscore = vx; dwhich = 0; }
-          if (vy > dual_tol && vy > dscore) { dscore = vy; dwhich = 1; }
-          if (vt > dual_tol && vt > dscore) { dscore = vt; dwhich = 2; }
-          if (fz > fzm + feas_tol && !top) { ntop = 1; add = true; }
-          if (fz < -feas_tol) { napex = 1; add = true; }
-          else {
-            if (sx == 0) { if (-fx - mu * fz > feas_tol) { nsx = -1; add = true; } else if (fx - mu * fz > feas_tol) { nsx = 1; add = true; } }
-            if (sy == 0) { if (-fy - mu * fz > feas_tol) { nsy = -1; add = true; } else if (fy - mu * fz > feas_tol) { nsy = 1; add = true; } }
-          }
-        }
-        // drops: all of them in the fast rounds
-        if (round < 3) {
-          if (apex) {
-            if (dwhich == 3) {
-              napex = 0; ntop = 0;
-              nsx = gx > 0 ? -1 : (gx < 0 ? 1 : 0);
-              nsy = gy > 0 ? -1 : (gy < 0 ? 1 : 0);
-            }
-          } else {
-            const double gvz = gz + mu * (sx * gx + sy * gy);
-            if (sx != 0 && nsx == sx && -(sx == -1 ? gx : -gx) > dual_tol) nsx = 0;
-            if (sy != 0 && nsy == sy && -(sy == -1 ? gy : -gy) > dual_tol) nsy = 0;
-            if (top && ntop == top && gvz > dual_tol) ntop = 0;
-          }
-        }
+        gxb = hu[3 * b] + gs[3 * b]; gyb = hu[3 * b + 1] + gs[3 * b + 1];
+        fs = face_step(face[4 * b], face[4 * b + 1], face[4 * b + 2], face[4 * b + 3], gxb, gyb, hu[3 * b + 2] + gs[3 * b + 2],
+                       dua[3 * b], dua[3 * b + 1], dua[3 * b + 2], mu, fzm, dual_tol, feas_tol, round < 3);
       }
       if (round >= 3) {
-        const bool any_add = __any_sync(0xffffffffu, add);
-        const double dmax = wmax(dscore);
-        if (!any_add && lane < nb && dwhich >= 0 && dscore == dmax) {
-          if (dwhich == 0) nsx = 0;
-          else if (dwhich == 1) nsy = 0;
-          else if (dwhich == 2) ntop = 0;
-          else {
-            const double gx = hu[3 * lane] + gs[3 * lane], gy = hu[3 * lane + 1] + gs[3 * lane + 1];
-            napex = 0; ntop = 0;
-            nsx = gx > 0 ? -1 : (gx < 0 ? 1 : 0);
-            nsy = gy > 0 ? -1 : (gy < 0 ? 1 : 0);
-          }
-        }
+        const bool any_add = __any_sync(0xffffffffu, fs.add);
+        const double dmax = wmax(fs.dscore);
+        if (!any_add && lane < nb && fs.dwhich >= 0 && fs.dscore == dmax) face_single_drop(fs, gxb, gyb);
       }
       if (lane < nb) {
-        if (nsx != sx || nsy != sy || ntop != top || napex != apex) changed = 1;
         const int b = lane;
-        face[4 * b] = (signed char)nsx; face[4 * b + 1] = (signed char)nsy; face[4 * b + 2] = (signed char)ntop; face[4 * b + 3] = (signed char)napex;
+        if (fs.sx != face[4 * b] || fs.sy != face[4 * b + 1] || fs.top != face[4 * b + 2] || fs.apex != face[4 * b + 3]) changed = 1;
+        face[4 * b] = (signed char)fs.sx; face[4 * b + 1] = (signed char)fs.sy; face[4 * b + 2] = (signed char)fs.top; face[4 * b + 3] = (signed char)fs.apex;
       }
       const bool any_changed = __any_sync(0xffffffffu, changed);
       // NaN compares false everywhere above: a non-finite solve must never pass as verified
