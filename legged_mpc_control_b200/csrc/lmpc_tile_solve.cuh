@@ -522,7 +522,9 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
       const double mub = sz * inv_m;
       if (!(rdinf == rdinf) || !(mub == mub)) { ipm_broken = true; break; }
       if (rdinf <= rdt && mub <= mu_tol) {
-        // convergence claimed on the recursively updated H u: confirm with an exact product on H
+        // stages 0 and 1 hand over to the exact polish, which verifies KKT on H itself (see solve_one_warp);
+        // the last stage confirms the claim made on the recursively updated H u with an exact product on H
+        if (stage < 2) { ipm_converged = true; break; }
         for (int b = lane; b < nb; b += 32) {
           double hd[6];
 #pragma unroll

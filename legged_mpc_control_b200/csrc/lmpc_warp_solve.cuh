@@ -445,8 +445,11 @@ static __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpSt
       const double mub = sz * inv_m;
       if (!(rdinf == rdinf) || !(mub == mub)) { ipm_broken = true; break; }
       if (rdinf <= rdt && mub <= mu_tol) {
-        // convergence claimed on the recursively updated H u: confirm with an exact product on H
-        // itself (subtracting W u from M u would cancel catastrophically: W ~ z/s is huge here)
+        // Stages 0 and 1 hand over to the exact polish, which verifies KKT on H itself: the claim needs no
+        // confirmation there (one H*x saved per solve).  The last stage returns the interior-point iterate
+        // as the answer, so there convergence claimed on the recursively updated H u is confirmed with an
+        // exact product (subtracting W u from M u would cancel catastrophically: W ~ z/s is huge here).
+        if (stage < 2) { ipm_converged = true; break; }
         if (act) {
           __stcg(Hg + moff[0], hd[0]); __stcg(Hg + moff[4], hd[3]); __stcg(Hg + moff[8], hd[5]);
           __stcg(Hg + moff[1], hd[1]); __stcg(Hg + moff[3], hd[1]);

@@ -252,12 +252,15 @@ __device__ __forceinline__ double2 wm_diag8_mma(double ax, double ay) {
   const double b = __shfl_sync(0xffffffffu, ay, 9 * t);
   const double d = __shfl_sync(0xffffffffu, ay, 9 * t + 4);
   const double nan_ = __longlong_as_double(0x7ff8000000000000ll);
-  const double ra = (a > 0.0) ? frsqrt(a) : nan_;    // 1 / l11
-  const double ia = ra * ra;                         // 1 / a
-  const double sc = fma(-b * ia, b, d);              // l22^2 = d - b^2 / a
-  const double rs = (sc > 0.0) ? frsqrt(sc) : nan_;  // 1 / l22
-  const double gx = ra * fx;                         // G'[n][2t]   = G[2t][n]
-  const double gy = rs * fma(-(b * ia), fx, fy);     // G'[n][2t+1] = G[2t+1][n]
+  // 1/l11 = rsqrt(a);  l22^2 = det / a with det = a d - b^2, so 1/l22 = rsqrt(det) sqrt(a) = rsqrt(det) a rsqrt(a):
+  // the two reciprocal square roots do not depend on each other and run side by side
+  const double det = fma(a, d, -b * b);
+  const double ra = (a > 0.0) ? frsqrt(a) : nan_;      // 1 / l11
+  const double rd = (det > 0.0) ? frsqrt(det) : nan_;
+  const double ia = ra * ra;                           // 1 / a
+  const double rs = rd * (a * ra);                     // 1 / l22
+  const double gx = ra * fx;                           // G'[n][2t]   = G[2t][n]
+  const double gy = rs * fma(-(b * ia), fx, fy);       // G'[n][2t+1] = G[2t+1][n]
   double2 G = make_double2(0.0, 0.0);
   dmma(G, (g == 2 * t) ? 1.0 : 0.0, gx);
   dmma(G, (g == 2 * t + 1) ? 1.0 : 0.0, gy);
