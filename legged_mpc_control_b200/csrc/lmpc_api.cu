@@ -189,7 +189,9 @@ extern "C" void lmpc_destroy(lmpc_handle* h) {
 // Launch classify + the per-size-class solves on `s` for the device-resident batch `kb`.  Every
 // solve kernel is enqueued right behind the classification and reads its class size on the device:
 // no host synchronisation.  A class is launched only if the horizon can produce it (n <= 12 H).
-static lmpc_status launch_solve(lmpc_handle* h, KBatch kb, cudaStream_t s) {
+// class_mask: bit c set = size class c may be non-empty (host-pointer calls know the contact rows and skip
+// the launches of the classes no problem falls into; device-pointer calls pass ~0u).
+static lmpc_status launch_solve(lmpc_handle* h, KBatch kb, cudaStream_t s, unsigned class_mask = ~0u) {
   const int H = h->kp.H;
   kb.warm = h->warm_enabled ? (uint8_t*)h->d_warm.p : nullptr;
   kb.warm_shift = h->warm_shift;
@@ -205,22 +207,24 @@ static lmpc_status launch_solve(lmpc_handle* h, KBatch kb, cudaStream_t s) {
   h->launches++;
   const lmpc::LaunchCtx c{h->device, &h->kp, dstats, h->num_sms, s, &h->launches};
   const int nmax = 12 * H;  // largest reduced dimension this horizon can produce
-  lmpc_status st = h->kp.class0_on_tiles ? lmpc::launch_tile8(c, kb, &h->d_wsA, order, cnt + 0, ctr + 0, 1)
-                                         : lmpc::launch_warp_class(c, kb, &h->d_wsA, order, cnt + 0, ctr + 0);
+  lmpc_status st = LMPC_OK;
+  if (class_mask & 1u)
+    st = h->kp.class0_on_tiles ? lmpc::launch_tile8(c, kb, &h->d_wsA, order, cnt + 0, ctr + 0, 1)
+                               : lmpc::launch_warp_class(c, kb, &h->d_wsA, order, cnt + 0, ctr + 0);
   if (st != LMPC_OK) return st;
-  if (nmax > lmpc::kWarpNMax) {
+  if (nmax > lmpc::kWarpNMax && (class_mask & 2u)) {
     st = lmpc::launch_tile15(c, kb, &h->d_wsT1, order + stride, cnt + 1, ctr + 1, h->tune.tile_nw);
     if (st != LMPC_OK) return st;
   }
-  if (nmax > 8 * lmpc::kTileA) {
+  if (nmax > 8 * lmpc::kTileA && (class_mask & 4u)) {
     st = lmpc::launch_tile24(c, kb, &h->d_wsT2, order + 2 * stride, cnt + 2, ctr + 2, h->tune.tile_nw);
     if (st != LMPC_OK) return st;
   }
-  if (nmax > 8 * lmpc::kTileB) {  // class 4 (192 < n <= 288)
+  if (nmax > 8 * lmpc::kTileB && (class_mask & 16u)) {  // class 4 (192 < n <= 288)
     st = lmpc::launch_tile36(c, kb, &h->d_wsT3, order + 4 * stride, cnt + 4, ctr + 4, 0);
     if (st != LMPC_OK) return st;
   }
-  if (nmax > 8 * lmpc::kTileD) {  // class 3 (n > 288): only horizons above 24 reach it
+  if (nmax > 8 * lmpc::kTileD && (class_mask & 8u)) {  // class 3 (n > 288): only horizons above 24 reach it
     st = lmpc::launch_tile48(c, kb, &h->d_ws, order + 3 * stride, cnt + 3, ctr + 3, 0);
     if (st != LMPC_OK) return st;
   }
@@ -329,9 +333,15 @@ extern "C" lmpc_status lmpc_solve(lmpc_handle* h, int32_t batch, const lmpc_batc
     kb.cmd = (const double*)(di + o_cmd); kb.contact = di + o_con;
     kb.grf = (double*)(dout + p_grf); kb.status = (int*)(dout + p_st); kb.iters = (int*)(dout + p_it);
     kb.active = (uint32_t*)(dout + p_act); kb.B = batch;
+    unsigned mask = 0u;  // a single robot's tick launches classify + ONE solve kernel instead of up to five
+    for (size_t i = 0; i < nb; ++i) {
+      int n = 0;
+      for (int t = 0; t < 4 * Hh; ++t) n += in->contact[i * 4 * Hh + t] ? 3 : 0;
+      mask |= 1u << lmpc::size_class(n);
+    }
     void* saved = h->d_stats.p;  // the statistics block rides at the head of the packed output
     h->d_stats.p = dout;
-    st = launch_solve(h, kb, s);
+    st = launch_solve(h, kb, s, mask);
     h->d_stats.p = saved;
     if (st != LMPC_OK) return st;
     CK(cudaMemcpyAsync(h->h_pout, dout, out_bytes, cudaMemcpyDeviceToHost, s));
