@@ -69,7 +69,8 @@ static lmpc_status launch_tile_nw(const LaunchCtx& c, const KBatch& kb, DevBuf* 
 }
 
 // Warps per QP, measured (C3 / reference preset, solves/s): NT=15: 598k / 647k / 519k at 1 / 2 / 4 warps
-// (4 warps cost the third CTA per SM); NT=24: 90k / 106k / 146k (one CTA per SM anyway); NT=36/48: 4.
+// (4 warps cost the third CTA per SM); NT=24: 90k / 106k / 141k / 150k at 1 / 2 / 4 / 8 warps (one CTA per SM anyway);
+// NT=36/48: 4.
 #if LMPC_TILE_NT == 8
 // experiment: the rolled tile code at the one-warp size, one warp per QP — an A/B against
 // solve_warp_kernel's straight-line code for the instruction-cache question
@@ -85,9 +86,10 @@ lmpc_status launch_tile15(const LaunchCtx& c, const KBatch& kb, DevBuf* ws, cons
 }
 #elif LMPC_TILE_NT == 24
 lmpc_status launch_tile24(const LaunchCtx& c, const KBatch& kb, DevBuf* ws, const int* order, const int* count, int* work, int nw) {
-  if (nw == 0) nw = 4;
+  if (nw == 0) nw = 8;  // one CTA per SM either way (154 KB factor): 8 warps give every scheduler a second warp, +6 % over 4
   if (nw == 1) return launch_tile_nw<24, 1>(c, kb, ws, order, count, work);
   if (nw == 2) return launch_tile_nw<24, 2>(c, kb, ws, order, count, work);
+  if (nw == 8) return launch_tile_nw<24, 8>(c, kb, ws, order, count, work);
   return launch_tile_nw<24, 4>(c, kb, ws, order, count, work);
 }
 #elif LMPC_TILE_NT == 36

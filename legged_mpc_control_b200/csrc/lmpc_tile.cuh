@@ -164,6 +164,10 @@ __device__ __forceinline__ bool gm_factor_mw(const double* Mg, double* Ls, doubl
   if (NW >= 2 && w == 1) return gm_factor_mw_w<NT, FROM_G, NW, (NW >= 2 ? 1 : 0)>(Mg, Ls, xb, nte);
   if (NW >= 4 && w == 2) return gm_factor_mw_w<NT, FROM_G, NW, (NW >= 4 ? 2 : 0)>(Mg, Ls, xb, nte);
   if (NW >= 4 && w == 3) return gm_factor_mw_w<NT, FROM_G, NW, (NW >= 4 ? 3 : 0)>(Mg, Ls, xb, nte);
+  if (NW >= 8 && w == 4) return gm_factor_mw_w<NT, FROM_G, NW, (NW >= 8 ? 4 : 0)>(Mg, Ls, xb, nte);
+  if (NW >= 8 && w == 5) return gm_factor_mw_w<NT, FROM_G, NW, (NW >= 8 ? 5 : 0)>(Mg, Ls, xb, nte);
+  if (NW >= 8 && w == 6) return gm_factor_mw_w<NT, FROM_G, NW, (NW >= 8 ? 6 : 0)>(Mg, Ls, xb, nte);
+  if (NW >= 8 && w == 7) return gm_factor_mw_w<NT, FROM_G, NW, (NW >= 8 ? 7 : 0)>(Mg, Ls, xb, nte);
   return gm_factor_mw_w<NT, FROM_G, NW, 0>(Mg, Ls, xb, nte);
 }
 // Job mailbox of the CTA: 0 exit, 1 factor from the L2 workspace, 2 factor in place, 3 Hessian

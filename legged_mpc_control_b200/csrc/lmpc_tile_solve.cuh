@@ -220,7 +220,7 @@ __device__ __forceinline__ void tile_solve(const double* Ls, double* x, int nte)
   // Measured (solves/s, one-warp solve vs blocked over the CTA): NT=15 C3 618k vs 535k, NT=24 trot H=30 139k vs
   // 137k (shared-memory factor: the barriers cost what the parallel rows save); NT=36/48 all-gait H=30 43.6k vs
   // 50.6k (factor in L2: four warps keep four times as many 400-cycle loads in flight).  So only the L2 classes.
-  if (NW == 1 || NT <= 24) { gm_solve<NT>(Ls, x, nte); return; }
+  if (NW == 1 || (NT <= 24 && NW < 8)) { gm_solve<NT>(Ls, x, nte); return; }
   if ((threadIdx.x & 31) == 0) {
     TileJobArgs* a = tile_job_args();
     a->y = x; a->nte = nte;
