@@ -103,6 +103,8 @@ static void fill_kparams(const lmpc_params& p, KParams* k) {
   if (const char* e = getenv("LMPC_TRY_INTERIOR")) k->try_interior = atoi(e);
   k->class0_on_tiles = 0;
   if (const char* e = getenv("LMPC_CLASS0_TILES")) k->class0_on_tiles = atoi(e);
+  k->l2_persist = 0;
+  if (const char* e = getenv("LMPC_L2_PERSIST")) k->l2_persist = atoi(e);
   k->warp_occ_cap = 0;
   if (const char* e = getenv("LMPC_WARP_OCC")) k->warp_occ_cap = atoi(e);
   k->tma_prefetch = 0;
@@ -155,6 +157,11 @@ extern "C" lmpc_status lmpc_create(const lmpc_params* params, int32_t max_batch,
   if (const char* e = getenv("LMPC_TILE_NW")) h->tune.tile_nw = atoi(e);
   h->tune.debug_stats = getenv("LMPC_DEBUG_STATS") != nullptr;
   memset(&h->last_stats, 0, sizeof(KStats));
+  if (h->kp.l2_persist) {
+    cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)prop.persistingL2CacheMaxSize);
+    if (h->tune.debug_stats)
+      fprintf(stderr, "[lmpc] persisting L2: max %d MB, window max %d MB\n", prop.persistingL2CacheMaxSize >> 20, prop.accessPolicyMaxWindowSize >> 20);
+  }
   st = create_resources(h);
   if (st == LMPC_OK && params->solver == LMPC_SOLVER_ACTIVE_SET) st = lmpc_set_warm_start(h, 1, 1);  // the face records are this solver's state
   if (st != LMPC_OK) {  // nothing leaks: the handle, its stream, events and buffers go through lmpc_destroy

@@ -1,4 +1,6 @@
 // lmpc_k_warp.cu — size class 0 (n <= 63): persistent one-warp-per-QP solve and its launcher.
+#include <string.h>
+
 #include "lmpc_internal.h"
 #include "lmpc_warp_solve.cuh"
 
@@ -104,6 +106,16 @@ static lmpc_status launch_warp_r(const LaunchCtx& c, const KBatch& kb, DevBuf* w
   int grid = c.num_sms * occ;
   if (grid > kb.B) grid = kb.B;
   CK(ws->ensure((size_t)grid * WN * WN * sizeof(double)));
+  if (c.kp->l2_persist) {  // experiment: pin the Hessian workspace in L2 (persisting access-policy window on the launch stream)
+    cudaStreamAttrValue av;
+    memset(&av, 0, sizeof(av));
+    av.accessPolicyWindow.base_ptr = ws->p;
+    av.accessPolicyWindow.num_bytes = (size_t)grid * WN * WN * sizeof(double);
+    av.accessPolicyWindow.hitRatio = 1.0f;
+    av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+    av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+    CK(cudaStreamSetAttribute(c.stream, cudaStreamAttributeAccessPolicyWindow, &av));
+  }
   KBatch k = kb;
   k.order = order;
   solve_warp_kernel<<<grid, 32, wp.total_bytes, c.stream>>>(*c.kp, k, c.stats, (double*)ws->p, count, work);

@@ -21,6 +21,7 @@ struct KParams {
   int sigma_pow;    // exponent of the Mehrotra centering rule (3)
   int try_interior; // experiment: cold problems first try the polish from all-interior faces
   int class0_on_tiles; // experiment: run size class 0 on solve_tile_kernel<8,1> (rolled code) instead of solve_warp_kernel
+  int l2_persist;   // experiment: persisting-L2 access window over the one-warp kernel's Hessian workspace
   int warp_occ_cap; // experiment: cap on resident warps per SM of the one-warp kernel (0 = none)
   int tma_prefetch; // experiment: stage the NEXT problem's x0/foot records by TMA bulk copy while this one solves
   double inertia[9];
