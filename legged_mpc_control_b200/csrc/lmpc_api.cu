@@ -181,7 +181,7 @@ extern "C" void lmpc_destroy(lmpc_handle* h) {
   DevBuf* bufs[] = {&h->d_x0, &h->d_rot, &h->d_foot, &h->d_cmd, &h->d_contact, &h->d_q, &h->d_r, &h->d_mu,
                     &h->d_fz, &h->d_mass, &h->d_inertia, &h->d_grf, &h->d_status, &h->d_iters, &h->d_active,
                     &h->d_U, &h->d_stats, &h->d_counter, &h->d_ws, &h->d_wsA, &h->d_wsT1, &h->d_wsT2, &h->d_wsT3, &h->d_order, &h->d_warm,
-                    &h->d_pin, &h->d_pout, &h->d_rx, &h->d_rfw, &h->d_rph, &h->d_rgait, &h->d_rspeed, &h->d_rtot, &h->d_xlog, &h->d_glog, &h->d_rfsm};
+                    &h->d_pin, &h->d_pout, &h->d_rx, &h->d_rfw, &h->d_rph, &h->d_rgait, &h->d_rspeed, &h->d_rtot, &h->d_xlog, &h->d_glog, &h->d_rfsm, &h->d_aux};
   for (DevBuf* b : bufs) b->release();
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);

@@ -123,31 +123,39 @@ __global__ void tau_ctrl_kernel(const __grid_constant__ LegDev D, const __grid_c
   for (int a = 0; a < 3; ++a) { D.ang_tgt[o3 + a] = ang[a]; D.vel_tgt[o3 + a] = vel[a]; }
 }
 
-// Host-pointer calls: every non-NULL array is staged through one device buffer per call.
+// Host-pointer calls: every non-NULL array is staged through ONE handle-owned device buffer
+// (h->d_aux, grown on demand and kept), carved into 256-byte aligned slices; no cudaMalloc per call
+// once the buffer has reached the batch's size.
 struct Stager {
   lmpc_handle* h;
-  std::vector<void*> dev;
   struct Out { void* host; void* dev; size_t bytes; };
   std::vector<Out> outs;
   bool on_device;
+  size_t used = 0;
   cudaError_t err = cudaSuccess;
-  Stager(lmpc_handle* h_, bool dev_) : h(h_), on_device(dev_) {}
-  ~Stager() { for (void* p : dev) cudaFree(p); }
+  // upper_bound: bytes of every array the call can stage plus 256 per array of alignment slack
+  Stager(lmpc_handle* h_, bool dev_, size_t upper_bound) : h(h_), on_device(dev_) {
+    if (!on_device) err = h->d_aux.ensure(upper_bound);
+  }
+  void* carve(size_t bytes) {
+    if (err != cudaSuccess) return nullptr;
+    const size_t at = (used + 255) & ~(size_t)255;
+    if (at + bytes > h->d_aux.cap) { err = cudaErrorMemoryAllocation; return nullptr; }
+    used = at + bytes;
+    return (char*)h->d_aux.p + at;
+  }
   template <class T>
   T* in(const T* host, size_t n) {
     if (!host || on_device) return const_cast<T*>(host);
-    void* d = nullptr;
-    if (err == cudaSuccess) err = cudaMalloc(&d, n * sizeof(T));
-    if (err == cudaSuccess) { dev.push_back(d); err = cudaMemcpyAsync(d, host, n * sizeof(T), cudaMemcpyHostToDevice, h->stream); }
+    void* d = carve(n * sizeof(T));
+    if (d) err = cudaMemcpyAsync(d, host, n * sizeof(T), cudaMemcpyHostToDevice, h->stream);
     return (T*)d;
   }
   template <class T>
   T* out(T* host, size_t n, bool also_in = false) {
     if (!host || on_device) return host;
-    void* d = nullptr;
-    if (err == cudaSuccess) err = cudaMalloc(&d, n * sizeof(T));
-    if (err == cudaSuccess) {
-      dev.push_back(d);
+    void* d = carve(n * sizeof(T));
+    if (d) {
       outs.push_back({host, d, n * sizeof(T)});
       if (also_in) err = cudaMemcpyAsync(d, host, n * sizeof(T), cudaMemcpyHostToDevice, h->stream);
     }
@@ -181,7 +189,8 @@ static lmpc_status fsm_call(lmpc_handle* h, int32_t batch, double dt, const lmpc
   }
   CK(cudaSetDevice(h->device));
   const size_t B = (size_t)batch, H = (size_t)h->kp.H;
-  lmpc::Stager s(h, io->on_device != 0);
+  // 5 per-leg state arrays (<= 8 B), gait + speed, contact flag, plan, table; 16 arrays of slack
+  lmpc::Stager s(h, io->on_device != 0, B * (4 * 8 * 4 + 4 * 4 * 2 + 4 + 8 + 4 * 8 + 4 + 4 * H) + 16 * 256);
   lmpc::FsmDev D;
   D.phase = s.out(io->gait_phase, 4 * B, true); D.state = s.out(io->fsm_state, 4 * B, true); D.index = s.out(io->fsm_index, 4 * B, true);
   D.start = s.out(io->fsm_start, 4 * B, true); D.end = s.out(io->fsm_end, 4 * B, true);
@@ -223,7 +232,8 @@ static lmpc_status leg_call(lmpc_handle* h, int32_t batch, const lmpc_leg_geomet
   }
   CK(cudaSetDevice(h->device));
   const size_t B = (size_t)batch;
-  lmpc::Stager s(h, io->on_device != 0);
+  // <= 16 arrays of 12 doubles, j_foot (36), rot (9), three 3-vectors, mode; 32 arrays of slack
+  lmpc::Stager s(h, io->on_device != 0, B * 8 * (12 * 16 + 36 + 9 + 3 * 3 + 1) + 32 * 256);
   lmpc::LegDev D;
   memset(&D, 0, sizeof(D));
   D.joint_pos = s.in(io->joint_pos, 12 * B); D.joint_vel = s.in(io->joint_vel, 12 * B); D.rot = s.in(io->rot, 9 * B);

@@ -105,6 +105,7 @@ struct lmpc_handle {
   // closed-loop rollout state (lmpc_rollout)
   lmpc::DevBuf d_rx, d_rfw, d_rph, d_rgait, d_rspeed, d_rtot, d_xlog, d_glog, d_rfsm;
   cudaEvent_t ev_r0 = nullptr, ev_r1 = nullptr;
+  lmpc::DevBuf d_aux;  // staging of the host-pointer FSM / leg-kinematics / torque-map calls (lmpc_aux.cu)
   Tuning tune;
   lmpc::KStats last_stats;
   float last_ms = 0.f;
