@@ -55,7 +55,8 @@ enum {
   LMPC_PROB_OK = 0,          /* exact active-set solution, KKT verified on device */
   LMPC_PROB_OK_IPM_ONLY = 1, /* converged by interior point to tight tolerance, no exact polish */
   LMPC_PROB_MAX_ITER = 2,    /* not converged: grf zeroed (reference NaN rule, ConvexQPSolver.cpp:321-326) */
-  LMPC_PROB_NON_FINITE = 3   /* non-finite input or iterate: grf zeroed */
+  LMPC_PROB_NON_FINITE = 3,  /* non-finite input or iterate: grf zeroed */
+  LMPC_PROB_TOO_LARGE = 4    /* lmpc_solve_noalloc only: reduced dimension n > 63, not solved, grf zeroed */
 };
 
 enum { LMPC_DISC_EULER = 0, LMPC_DISC_ZOH = 1 };
@@ -170,6 +171,32 @@ lmpc_status lmpc_solve(lmpc_handle* h, int32_t batch, const lmpc_batch_in* in,
 lmpc_status lmpc_solve_async(lmpc_handle* h, int32_t batch, const lmpc_batch_in* in,
                              const lmpc_batch_out* out, void* cuda_stream);
 lmpc_status lmpc_wait(lmpc_handle* h);
+
+/* Allocation-free solve.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc on the call path (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).  It runs a variant of the one-warp-per-QP
+ * kernel (size class 0) whose scratch memory — per-warp Hessian slots, work counter, statistics —
+ * is a file-scope `static __device__` array of fixed size in liblmpc.so instead of the handle's
+ * cudaMalloc'ed workspaces: 256 B + 148 slots x 32 KiB = 4 849 920 B (4.63 MiB), held by every GPU
+ * that loads the library until the process exits.  The call issues one cudaMemsetAsync (256 B) and
+ * one kernel launch on `cuda_stream` (a cudaStream_t; NULL = the handle's stream) and calls no
+ * cudaMalloc, cudaFree or allocating library routine; the first call on a device also looks up the
+ * array's device address (cudaGetSymbolAddress) — make that call once before any graph capture.
+ * Limits, rejected with LMPC_ERR_INVALID_ARG and a message:
+ *   batch <= LMPC_NOALLOC_MAX_BATCH;  device pointers only (in->on_device and out->on_device set);
+ * and per problem: a reduced dimension n = 3 x (stance leg-steps) above 63 is not solved — status
+ * LMPC_PROB_TOO_LARGE, grf / U / active_set zeroed (H <= 5 can never exceed it; trot, bound and pronk
+ * at H = 10 have n = 60).  The handle supplies the parameters, device and default stream only; warm
+ * start is not used and lmpc_last_* / lmpc_wait do not see this call.
+ * blocking != 0: waits for the result and returns LMPC_ERR_NOT_CONVERGED if any problem ended with
+ * status >= 2; blocking == 0: returns after the launch, the caller synchronises the stream and reads
+ * status[].  Results are the same exact minimisers lmpc_solve returns.
+ * ALL calls on a device share the one array, which keeps the previous call's contents (the call
+ * clears the part that must start at zero): two calls that overlap on the GPU — different streams,
+ * or two host threads — race.  Serialise them. */
+#define LMPC_NOALLOC_MAX_BATCH 4096
+lmpc_status lmpc_solve_noalloc(lmpc_handle* h, int32_t batch, const lmpc_batch_in* in,
+                               const lmpc_batch_out* out, void* cuda_stream, int32_t blocking);
 
 /* Warm start (OSQP `setWarmStart(true)` analogue, ConvexQPSolver.cpp:185).  When enabled, every
  * solve stores the pyramid face of each stance block of problem i (device resident, 4H+4 bytes per

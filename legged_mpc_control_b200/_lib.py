@@ -45,6 +45,7 @@ def lib():
     L.lmpc_solve.argtypes = [C.c_void_p, C.c_int32, C.POINTER(abi.LmpcBatchIn), C.POINTER(abi.LmpcBatchOut)]
     L.lmpc_solve_async.argtypes = [C.c_void_p, C.c_int32, C.POINTER(abi.LmpcBatchIn), C.POINTER(abi.LmpcBatchOut), C.c_void_p]
     L.lmpc_wait.argtypes = [C.c_void_p]
+    L.lmpc_solve_noalloc.argtypes = [C.c_void_p, C.c_int32, C.POINTER(abi.LmpcBatchIn), C.POINTER(abi.LmpcBatchOut), C.c_void_p, C.c_int32]
     L.lmpc_reset_warm_start.argtypes = [C.c_void_p]
     L.lmpc_set_warm_start.argtypes = [C.c_void_p, C.c_int32, C.c_int32]
     L.lmpc_last_warm_hits.argtypes = [C.c_void_p]

@@ -12,7 +12,8 @@ MAX_HORIZON = 32
 NUM_LEG = 4
 
 OK, ERR_INVALID_ARG, ERR_CUDA, ERR_NO_DEVICE, ERR_NOT_CONVERGED, ERR_ALLOC = range(6)
-PROB_OK, PROB_OK_IPM_ONLY, PROB_MAX_ITER, PROB_NON_FINITE = range(4)
+PROB_OK, PROB_OK_IPM_ONLY, PROB_MAX_ITER, PROB_NON_FINITE, PROB_TOO_LARGE = range(5)
+NOALLOC_MAX_BATCH = 4096  # include/lmpc.h LMPC_NOALLOC_MAX_BATCH
 DISC_EULER, DISC_ZOH = 0, 1
 COST_REF_HALF, COST_NS_TWO = 0, 1
 PREC_F64, PREC_F32 = 0, 1

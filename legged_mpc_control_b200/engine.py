@@ -93,6 +93,25 @@ class ConvexMpcEngine:
             return self.wait()
         return st
 
+    def solve_device_noalloc(self, ptrs_in: dict, ptrs_out: dict, batch: int, stream: int = 0, blocking: bool = True) -> int:
+        """lmpc_solve_noalloc (include/lmpc.h): the one-warp solve on the library's static device
+        scratch — no allocation on the call path.  Device pointers as in solve_device; batch <=
+        abi.NOALLOC_MAX_BATCH; problems with n > 63 come back with status PROB_TOO_LARGE.  Returns
+        OK or ERR_NOT_CONVERGED (blocking), raises on every other error."""
+        sin = abi.LmpcBatchIn()
+        for name, *_ in abi.IN_FIELDS:
+            setattr(sin, name, ptrs_in.get(name))
+        sin.on_device = 1
+        sout = abi.LmpcBatchOut()
+        for name in ("grf", "status", "iters", "active_set", "U"):
+            setattr(sout, name, ptrs_out.get(name))
+        sout.on_device = 1
+        st = self._L.lmpc_solve_noalloc(self._h, int(batch), C.byref(sin), C.byref(sout),
+                                        C.c_void_p(stream) if stream else None, 1 if blocking else 0)
+        if st not in (abi.OK, abi.ERR_NOT_CONVERGED):
+            raise LmpcError(st, _lib.last_error())
+        return st
+
     def wait(self) -> int:
         st = self._L.lmpc_wait(self._h)
         if st not in (abi.OK, abi.ERR_NOT_CONVERGED):
