@@ -176,19 +176,9 @@ __device__ __forceinline__ int* tile_job() {
   __shared__ int job;
   return &job;
 }
-// What warp 0 calls in place of gm_factor.
 __device__ __forceinline__ int* tile_job_nte() {
   __shared__ int nte;
   return &nte;
-}
-template <int NT, int NW, bool FROM_G>
-__device__ __forceinline__ bool tile_factor(const double* Mg, double* Ls, double* xb, int nte) {
-  if (NW == 1) return gm_factor<NT, FROM_G>(Mg, Ls, xb, nte);
-  if ((threadIdx.x & 31) == 0) { *tile_job_nte() = nte; *tile_job() = FROM_G ? 1 : 2; }
-  __syncthreads();  // releases the helper warps; also publishes warp 0's writes of M
-  const bool ok = gm_factor_mw<NT, FROM_G, NW>(Mg, Ls, xb, 0, nte);
-  __syncwarp();
-  return ok;
 }
 // Solve L L' x = b in place on the (8 NT)-vector x in shared memory.  Row-oriented block
 // substitution in t-layout; the solved blocks are read back from x itself (every lane re-reads the
@@ -272,46 +262,95 @@ static __device__ __noinline__ void gm_solve(const double* Ls, double* x, int nt
 }
 
 // ---- the same solve spread over the NW warps of a CTA: blocked substitution with BS tile rows per
-// block.  Per block, warp 0 solves the BS x BS triangle (short chains), then all warps subtract the
-// block's contribution from the remaining rows (independent rows: one per warp at a time), two CTA
-// barriers per block.  Every warp of the CTA must call it.  x is in shared memory, t-layout.
-template <int NT, int NW>
-__device__ __forceinline__ void gm_solve_mw_impl(const double* Ls, double* x, const int nte, const int w) {
+// block and EXPLICITLY INVERTED diagonal blocks.  A plain blocked substitution leaves the BS x BS
+// triangle of every block to one warp (BS dependent rows, each two DMMA round trips) while the other
+// warps wait at the barrier: at NT = 24 with eight warps that was 42 % of all stall samples
+// (profiles/r02_v8_ncu_stalls_solve_tile24_kernel.txt).  So right after the factorization every
+// diagonal block L_bb (BS x BS tiles, lower triangular) is replaced IN PLACE by its inverse — one warp
+// per block, ~BS^3/6 tile products, no barrier inside — and the triangle becomes BS independent rows of
+// a small matrix-vector product, one per warp.
+//
+// Storage after gm_invert_blocks_mw: tiles (I, K) outside the diagonal blocks still hold L_IK; the
+// diagonal slots still hold inv(L_II); a slot (I, K), I > K, INSIDE a diagonal block holds the
+// TRANSPOSE of tile (I, K) of inv(L_bb) (that is what the DMMA product X * Y' delivers without a
+// layout change: V_KI = -(sum_{k=K}^{I-1} V_Kk L_Ik') inv(L_II)',  V_KK = inv(L_KK)').
+constexpr int kTileSolveBS = 4;
+
+template <int NT, int BS>
+__device__ __forceinline__ void gm_block_inverse(double* Ls, int d0, int d1) {
   using G = TileGeom<NT>;
-  constexpr int BS = 4;
+  const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  double2* Lf = reinterpret_cast<double2*>(Ls) + lane;
+#pragma unroll
+  for (int a = 0; a < BS - 1; ++a) {  // tile column K = d0 + a of the block, left to right (columns > K still hold L)
+    const int K = d0 + a;
+    if (K < d1 - 1) {
+      double2 v[BS];  // v[c] = V_{K, d0 + c}
+      v[a] = tile_ld_t(Ls + 64 * G::lcol(K), g, t);
+#pragma unroll
+      for (int b = a + 1; b < BS; ++b) {
+        const int I = d0 + b;
+        if (I < d1) {
+          double2 acc = make_double2(0.0, 0.0);
+#pragma unroll
+          for (int c = a; c < b; ++c) dmma_xyt(acc, v[c], Lf[32 * (G::lcol(d0 + c) + I - (d0 + c))]);
+          double2 x = make_double2(0.0, 0.0);
+          dmma_xyt(x, make_double2(-acc.x, -acc.y), Lf[32 * G::lcol(I)]);
+          v[b] = x;
+          Lf[32 * (G::lcol(K) + I - K)] = x;
+        }
+      }
+    }
+  }
+}
+// Every warp of the CTA calls it right after gm_factor_mw (whose last barrier made the factor visible).
+template <int NT, int NW>
+__device__ __forceinline__ void gm_invert_blocks_mw(double* Ls, int nte, int w) {
+  constexpr int BS = kTileSolveBS;
+  for (int d0 = BS * w; d0 < nte; d0 += BS * NW) gm_block_inverse<NT, BS>(Ls, d0, d0 + BS < nte ? d0 + BS : nte);
+  __syncthreads();
+}
+
+// L L' x = b on a factor prepared by gm_invert_blocks_mw; x and the scratch vector tt (8 NT doubles
+// each) in shared memory, t-layout.  Forward: y goes to tt, the running right-hand side stays in x;
+// backward: the running right-hand side is tt, the solution lands in x.  Two CTA barriers per block
+// and direction; every warp of the CTA must call it.
+template <int NT, int NW>
+__device__ __forceinline__ void gm_solve_mw_impl(const double* Ls, double* x, double* tt, const int nte, const int w) {
+  using G = TileGeom<NT>;
+  constexpr int BS = kTileSolveBS;
   const int lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
   const double2* Lf = reinterpret_cast<const double2*>(Ls) + lane;
   double2* xt = reinterpret_cast<double2*>(x) + t;
+  double2* yt = reinterpret_cast<double2*>(tt) + t;
   // forward
   for (int d0 = 0; d0 < nte; d0 += BS) {
     const int d1 = d0 + BS < nte ? d0 + BS : nte;
-    if (w == 0) {
-      for (int J = d0; J < d1; ++J) {
-        double p0 = 0.0, p1 = 0.0;
-        for (int K = d0; K < J; ++K) {
-          const double2 l = Lf[32 * (G::lcol(K) + J - K)];
-          const double2 y = xt[4 * K];
-          p0 = fma(l.x, y.x, p0);
-          p1 = fma(l.y, y.y, p1);
+    for (int J = d0 + w; J < d1; J += NW) {  // y_J = inv(L_bb)[J, :] r   (row J of the block inverse: transposed slots)
+      const double2 li = Lf[32 * G::lcol(J)];
+      const double2 rj = xt[4 * J];
+      double p0 = li.x * rj.x, p1 = li.y * rj.y;
+#pragma unroll
+      for (int u = 0; u < BS - 1; ++u) {
+        const int K = d0 + u;
+        if (K < J) {
+          const double2 c = tile_ld_t(Ls + 64 * (G::lcol(K) + J - K), g, t);
+          const double2 r = xt[4 * K];
+          p0 = fma(c.x, r.x, p0);
+          p1 = fma(c.y, r.y, p1);
         }
-        double2 r = xt[4 * J];
-        if (J > d0) {
-          const double2 s = quad_reduce_t(p0 + p1);
-          r.x -= s.x; r.y -= s.y;
-        }
-        const double2 li = Lf[32 * G::lcol(J)];
-        xt[4 * J] = quad_reduce_t(fma(li.x, r.x, li.y * r.y));
       }
+      yt[4 * J] = quad_reduce_t(p0 + p1);
     }
     __syncthreads();
-    for (int I = d1 + w; I < nte; I += NW) {  // x_I -= sum_{K in block} L_IK y_K
+    for (int I = d1 + w; I < nte; I += NW) {  // r_I -= sum_{K in block} L_IK y_K
       double p0 = 0.0, p1 = 0.0;
 #pragma unroll
       for (int u = 0; u < BS; ++u) {
         const int K = d0 + u;
         if (K < d1) {
           const double2 l = Lf[32 * (G::lcol(K) + I - K)];
-          const double2 y = xt[4 * K];
+          const double2 y = yt[4 * K];
           p0 = fma(l.x, y.x, p0);
           p1 = fma(l.y, y.y, p1);
         }
@@ -323,25 +362,25 @@ __device__ __forceinline__ void gm_solve_mw_impl(const double* Ls, double* x, co
     }
     __syncthreads();
   }
-  // backward: blocks from the bottom
-  for (int d1 = nte; d1 > 0; d1 -= BS) {
-    const int d0 = d1 - BS > 0 ? d1 - BS : 0;
-    if (w == 0) {
-      for (int J = d1 - 1; J >= d0; --J) {
-        const double* ct = Ls + 64 * G::lcol(J) + 16 * t + g;  // transposed reads of column J: tile (J + i, J) at ct[64 i], ct[64 i + 8]
-        double p0 = 0.0, p1 = 0.0;
-        for (int I = J + 1; I < d1; ++I) {
-          const double2 xi = xt[4 * I];
-          p0 = fma(ct[64 * (I - J)], xi.x, p0);
-          p1 = fma(ct[64 * (I - J) + 8], xi.y, p1);
+  // backward: blocks from the bottom; right-hand side in tt
+  const int dlast = ((nte - 1) / BS) * BS;
+  for (int d0 = dlast; d0 >= 0; d0 -= BS) {
+    const int d1 = d0 + BS < nte ? d0 + BS : nte;
+    for (int J = d0 + w; J < d1; J += NW) {  // x_J = inv(L_bb)'[J, :] y   (column J of the block inverse: direct slots)
+      const double2 c = tile_ld_t(Ls + 64 * G::lcol(J), g, t);
+      const double2 yj = yt[4 * J];
+      double p0 = c.x * yj.x, p1 = c.y * yj.y;
+#pragma unroll
+      for (int u = 1; u < BS; ++u) {
+        const int I = d0 + u;
+        if (I > J && I < d1) {
+          const double2 l = Lf[32 * (G::lcol(J) + I - J)];
+          const double2 y = yt[4 * I];
+          p0 = fma(l.x, y.x, p0);
+          p1 = fma(l.y, y.y, p1);
         }
-        double2 r = xt[4 * J];
-        if (J < d1 - 1) {
-          const double2 s = quad_reduce_t(p0 + p1);
-          r.x -= s.x; r.y -= s.y;
-        }
-        xt[4 * J] = quad_reduce_t(fma(ct[0], r.x, ct[8] * r.y));
       }
+      xt[4 * J] = quad_reduce_t(p0 + p1);
     }
     __syncthreads();
     for (int J = w; J < d0; J += NW) {  // y_J -= sum_{I in block} L_IJ' x_I
@@ -357,16 +396,16 @@ __device__ __forceinline__ void gm_solve_mw_impl(const double* Ls, double* x, co
         }
       }
       const double2 s = quad_reduce_t(p0 + p1);
-      double2 r = xt[4 * J];
+      double2 r = yt[4 * J];
       r.x -= s.x; r.y -= s.y;
-      xt[4 * J] = r;
+      yt[4 * J] = r;
     }
     __syncthreads();
   }
 }
 template <int NT, int NW>
-static __device__ __noinline__ void gm_solve_mw(const double* Ls, double* x, int nte, int w) {
-  gm_solve_mw_impl<NT, NW>(Ls, x, nte, w);
+static __device__ __noinline__ void gm_solve_mw(const double* Ls, double* x, double* tt, int nte, int w) {
+  gm_solve_mw_impl<NT, NW>(Ls, x, tt, nte, w);
 }
 
 // y = H x for the full-symmetric workspace (global, L2); x, y (8 NT)-vectors in shared memory.

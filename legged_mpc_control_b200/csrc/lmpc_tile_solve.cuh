@@ -11,7 +11,7 @@
 namespace lmpc {
 
 struct TilePlan {
-  int oLS, oU, oGS, oHU, oRD, oDUA, oDU, oZ, oQ, oIS, oPRM, oXB;  // doubles
+  int oLS, oU, oGS, oHU, oRD, oDUA, oDU, oZ, oQ, oIS, oPRM, oXB, oTT;  // doubles
   int oBW, oCOS, oSIN, oCS, oSS, oE, oAJ, oBJ;           // setup scratch, inside LS
   int n_doubles;
   int oBLK, oFACE, oBMAP, total_bytes;
@@ -51,6 +51,7 @@ __host__ __device__ inline TilePlan make_tile_plan(int H) {
   p.oIS = o; o += 5 * G::NBMAX + (G::NBMAX & 1);
   p.oPRM = o; o += 32;
   p.oXB = o; o += 64;
+  p.oTT = o; if (NT >= kTileSmemMaxNT) o += G::N;  // scratch vector of the multi-warp solve (classes that use it)
   p.n_doubles = o;
   int b = o * 8;
   p.oBLK = b; b += 2 * G::NBMAX;
@@ -214,20 +215,36 @@ __device__ __forceinline__ void tile_symv(const double* Hg, const double* x, dou
   gm_symv<NT>(Hg, x, y, nte, 0, NW);
   __syncthreads();
 }
-// L L' x = b with the substitution blocked over the warps of the CTA (job 6); x in shared memory.
+// Does this class run the triangular solves on all warps of the CTA (diagonal blocks of the factor inverted)?
+// Measured (solves/s, one-warp solve vs plain blocked substitution over the CTA): NT=15 C3 618k vs 535k, NT=24
+// with four warps trot H=30 139k vs 137k (shared-memory factor: the barriers cost what the parallel rows save);
+// NT=36/48 all-gait H=30 43.6k vs 50.6k (factor in L2).  With inverted diagonal blocks: see DESIGN.md §6.
 template <int NT, int NW>
-__device__ __forceinline__ void tile_solve(const double* Ls, double* x, int nte) {
-  // Measured (solves/s, one-warp solve vs blocked over the CTA): NT=15 C3 618k vs 535k, NT=24 trot H=30 139k vs
-  // 137k (shared-memory factor: the barriers cost what the parallel rows save); NT=36/48 all-gait H=30 43.6k vs
-  // 50.6k (factor in L2: four warps keep four times as many 400-cycle loads in flight).  So only the L2 classes.
-  if (NW == 1 || (NT <= 24 && NW < 8)) { gm_solve<NT>(Ls, x, nte); return; }
+__host__ __device__ constexpr bool tile_mw_solve() { return NW > 1 && !(NT <= 24 && NW < 8); }
+
+// What warp 0 calls in place of gm_factor: the factorization on all warps (job 1 / 2), followed by the in-place
+// inversion of the diagonal blocks when the class solves on all warps.
+template <int NT, int NW, bool FROM_G>
+__device__ __forceinline__ bool tile_factor(const double* Mg, double* Ls, double* xb, int nte) {
+  if (NW == 1) return gm_factor<NT, FROM_G>(Mg, Ls, xb, nte);
+  if ((threadIdx.x & 31) == 0) { *tile_job_nte() = nte; *tile_job() = FROM_G ? 1 : 2; }
+  __syncthreads();  // releases the helper warps; also publishes warp 0's writes of M
+  const bool ok = gm_factor_mw<NT, FROM_G, NW>(Mg, Ls, xb, 0, nte);
+  if (tile_mw_solve<NT, NW>()) gm_invert_blocks_mw<NT, NW>(Ls, nte, 0);
+  __syncwarp();
+  return ok;
+}
+// L L' x = b (job 6 on all warps, or one warp); x and the scratch vector tt in shared memory.
+template <int NT, int NW>
+__device__ __forceinline__ void tile_solve(const double* Ls, double* x, double* tt, int nte) {
+  if (!tile_mw_solve<NT, NW>()) { gm_solve<NT>(Ls, x, nte); return; }
   if ((threadIdx.x & 31) == 0) {
     TileJobArgs* a = tile_job_args();
     a->y = x; a->nte = nte;
     *tile_job() = 6;
   }
   __syncthreads();
-  gm_solve_mw<NT, NW>(Ls, x, nte, 0);
+  gm_solve_mw<NT, NW>(Ls, x, tt, nte, 0);
 }
 // Helper warps (1 .. NW-1) live here until warp 0 posts job 0.
 template <int NT, int NW>
@@ -238,14 +255,16 @@ __device__ __forceinline__ void tile_helper_loop(const KParams& P, const TilePla
     __syncthreads();
     const int job = *tile_job();
     if (job == 0) return;
-    if (job == 1) gm_factor_mw<NT, true, NW>(Hg, tile_ls<NT>(pl, smem, Hg), sd + pl.oXB, w, *tile_job_nte());
-    else if (job == 2) gm_factor_mw<NT, false, NW>(Hg, tile_ls<NT>(pl, smem, Hg), sd + pl.oXB, w, *tile_job_nte());
-    else {
+    if (job == 1 || job == 2) {
+      if (job == 1) gm_factor_mw<NT, true, NW>(Hg, tile_ls<NT>(pl, smem, Hg), sd + pl.oXB, w, *tile_job_nte());
+      else gm_factor_mw<NT, false, NW>(Hg, tile_ls<NT>(pl, smem, Hg), sd + pl.oXB, w, *tile_job_nte());
+      if (tile_mw_solve<NT, NW>()) gm_invert_blocks_mw<NT, NW>(tile_ls<NT>(pl, smem, Hg), *tile_job_nte(), w);
+    } else {
       const TileJobArgs a = *tile_job_args();
       if (job == 3) tile_hessian_blocks<NT>(P, pl, smem, Hg, a.nb, a.n, a.sc, a.im2, threadIdx.x, 32 * NW);
       else if (job == 4) tile_reduced_matrix<NT>(pl, smem, Hg, a.nb, a.n, a.mu, threadIdx.x, 32 * NW);
       else if (job == 5) gm_symv<NT>(Hg, a.x, a.y, a.nte, w, NW);
-      else { gm_solve_mw<NT, NW>(tile_ls<NT>(pl, smem, Hg), a.y, a.nte, w); continue; }  // job 6 ends on its own barrier
+      else { gm_solve_mw<NT, NW>(tile_ls<NT>(pl, smem, Hg), a.y, sd + pl.oTT, a.nte, w); continue; }  // job 6 ends on its own barrier
       __syncthreads();
     }
   }
@@ -569,7 +588,7 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
       }
       __syncwarp();
       if (!tile_factor<NT, NW, true>(Hg, Ls, xb, nte)) { ipm_broken = true; break; }
-      tile_solve<NT, NW>(Ls, dua, nte);
+      tile_solve<NT, NW>(Ls, dua, sd + pl.oTT, nte);
       __syncwarp();
       double tau = 0.0;
       for (int b = lane; b < nb; b += 32) {
@@ -614,7 +633,7 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
         }
       }
       __syncwarp();
-      tile_solve<NT, NW>(Ls, du, nte);
+      tile_solve<NT, NW>(Ls, du, sd + pl.oTT, nte);
       __syncwarp();
       double tau2 = 0.0;
       for (int b = lane; b < nb; b += 32) {
@@ -727,7 +746,7 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
       }
       __syncwarp();
       if (!tile_factor<NT, NW, false>(Hg, Ls, xb, nte)) break;
-      tile_solve<NT, NW>(Ls, du, nte);
+      tile_solve<NT, NW>(Ls, du, sd + pl.oTT, nte);
       for (int i = lane; i < N; i += 32) dua[i] = 0.0;
       __syncwarp();
       for (int b = lane; b < nb; b += 32) {
@@ -789,7 +808,7 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
         du[3 * b + 2] = (apex || top) ? 0.0 : -gzt;
       }
       __syncwarp();
-      tile_solve<NT, NW>(Ls, du, nte);
+      tile_solve<NT, NW>(Ls, du, sd + pl.oTT, nte);
       __syncwarp();
       for (int b = lane; b < nb; b += 32) {
         const int sx = face[4 * b], sy = face[4 * b + 1];

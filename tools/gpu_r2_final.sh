@@ -23,6 +23,6 @@ cap() {  # cap <mangled regex> <name> <kernel substring for the stall tool> <mai
   rm -f gpurun_out/${T}_ncu_$N.ncu-rep
 }
 cap solve_warp solve_warp_kernel solve_warp_kernel lmpc_warp_solve.cuh 65536 northstar_a1 3
-cap ILi24ELi4 solve_tile24_kernel solve_tile_kernelILi24ELi4 lmpc_tile_solve.cuh 4096 reference_a1 2 trot
+cap ILi24ELi8 solve_tile24_kernel solve_tile_kernelILi24ELi8 lmpc_tile_solve.cuh 4096 reference_a1 2 trot
 cap ILi48ELi4 solve_tile48_kernel solve_tile_kernelILi48ELi4 lmpc_tile_solve.cuh 2048 reference_a1 2 stand
 cap ILi15ELi2 solve_tile15_kernel solve_tile_kernelILi15ELi2 lmpc_tile_solve.cuh 16384 northstar_go1_h20 2
