@@ -6,7 +6,8 @@ import os
 from . import abi
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "liblmpc.so")
+# LMPC_LIB_PATH: another in-tree build of the same library (kernel A/B experiments, tools/gpu_r2_ab.sh)
+LIB_PATH = os.environ.get("LMPC_LIB_PATH") or os.path.join(_HERE, "liblmpc.so")
 _LIB = None
 
 EXPORTS = (

@@ -156,6 +156,7 @@ extern "C" lmpc_status lmpc_create(const lmpc_params* params, int32_t max_batch,
   h->smem_optin = (int)prop.sharedMemPerBlockOptin;
   if (const char* e = getenv("LMPC_TILE_NW")) h->tune.tile_nw = atoi(e);
   h->tune.debug_stats = getenv("LMPC_DEBUG_STATS") != nullptr;
+  if (const char* e = getenv("LMPC_HOST_LANES")) h->tune.host_lanes = atoi(e);
   memset(&h->last_stats, 0, sizeof(KStats));
   if (h->kp.l2_persist) {
     cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)prop.persistingL2CacheMaxSize);
@@ -174,8 +175,11 @@ extern "C" lmpc_status lmpc_create(const lmpc_params* params, int32_t max_batch,
   return LMPC_OK;
 }
 
+extern "C" void lmpc_destroy_sharded(lmpc_sharded* s);
 extern "C" void lmpc_destroy(lmpc_handle* h) {
   if (!h) return;
+  if (h->lanes) lmpc_destroy_sharded(h->lanes);
+  h->lanes = nullptr;
   cudaSetDevice(h->device);
   if (h->stream) cudaStreamSynchronize(h->stream);
   DevBuf* bufs[] = {&h->d_x0, &h->d_rot, &h->d_foot, &h->d_cmd, &h->d_contact, &h->d_q, &h->d_r, &h->d_mu,
@@ -298,6 +302,10 @@ extern "C" lmpc_status lmpc_wait(lmpc_handle* h) {
   return finish_solve(h, h->pending_stream);
 }
 
+// Slices smaller than this are not worth a launch of their own (a few waves of the persistent grid).
+static constexpr int kLaneMinSlice = 2048;
+static lmpc_status solve_host_lanes(lmpc_handle* h, int32_t batch, const lmpc_batch_in* in, const lmpc_batch_out* out);
+
 extern "C" lmpc_status lmpc_solve(lmpc_handle* h, int32_t batch, const lmpc_batch_in* in,
                                   const lmpc_batch_out* out) {
   lmpc_status st = check_io(h, batch, in, out);
@@ -365,6 +373,9 @@ extern "C" lmpc_status lmpc_solve(lmpc_handle* h, int32_t batch, const lmpc_batc
     }
     return LMPC_OK;
   }
+  // ---- large batch, host pointers: slices in flight on this device (copies under the neighbouring slice's solve)
+  if (!h->is_lane && h->tune.host_lanes > 1 && !h->warm_enabled && batch >= kLaneMinSlice * h->tune.host_lanes)
+    return solve_host_lanes(h, batch, in, out);
   // host pointers: stage through device buffers owned by the handle
   const int H = h->kp.H;
   const size_t B = (size_t)batch;
@@ -550,7 +561,46 @@ extern "C" lmpc_status lmpc_solve_sharded(lmpc_sharded* s, int32_t batch, const 
   return worst;
 }
 
-extern "C" int64_t lmpc_launch_count(const lmpc_handle* h) { return h ? h->launches : 0; }
+// Large host-pointer batch on ONE device: the batch is cut into contiguous slices, every slice owned by an
+// engine of its own on h->device (stream, staging buffers, workspace, counters), all driven through
+// lmpc_solve_sharded.  Slice k+1's H2D copies and slice k-1's D2H copies run on the copy engines while slice
+// k solves, and the persistent grid of slice k+1 takes over the SMs CTA by CTA as slice k's last problems
+// finish, so the tail of one slice is covered by the head of the next.  Same answers as the one-shot path
+// (every problem is independent and solved by the same kernels).
+static lmpc_status solve_host_lanes(lmpc_handle* h, int32_t batch, const lmpc_batch_in* in, const lmpc_batch_out* out) {
+  if (!h->lanes) {
+    std::vector<int32_t> dev((size_t)h->tune.host_lanes, (int32_t)h->device);
+    lmpc_sharded* s = nullptr;
+    const lmpc_status st = lmpc_create_sharded(&h->params, h->max_batch, dev.data(), (int32_t)dev.size(), &s);
+    if (st != LMPC_OK) return st;
+    for (lmpc_handle* e : s->eng) { e->is_lane = true; e->tune = h->tune; e->tune.host_lanes = 0; }
+    h->lanes = s;
+  }
+  lmpc_sharded* s = h->lanes;
+  const lmpc_status st = lmpc_solve_sharded(s, batch, in, out);
+  KStats tot;
+  memset(&tot, 0, sizeof(tot));
+  float ms = 0.f;
+  for (const lmpc_handle* e : s->eng) {
+    const KStats& k = e->last_stats;
+    tot.problems += k.problems; tot.sum_n += k.sum_n; tot.sum_fact += k.sum_fact; tot.sum_polish += k.sum_polish;
+    tot.not_ok += k.not_ok; tot.ipm_only += k.ipm_only; tot.warm_hits += k.warm_hits; tot.flops += k.flops;
+    tot.n_max = k.n_max > tot.n_max ? k.n_max : tot.n_max;
+    ms += e->last_ms;
+  }
+  h->last_stats = tot;
+  h->last_ms = ms;  // sum of the slices' device spans (they run back to back)
+  if (st == LMPC_ERR_NOT_CONVERGED)
+    set_err(std::to_string((unsigned long long)tot.not_ok) + " problem(s) did not converge (grf zeroed)");
+  return st;
+}
+
+extern "C" int64_t lmpc_launch_count(const lmpc_handle* h) {
+  if (!h) return 0;
+  int64_t n = h->launches;
+  if (h->lanes) for (const lmpc_handle* e : h->lanes->eng) n += e->launches;
+  return n;
+}
 extern "C" float lmpc_last_kernel_ms(const lmpc_handle* h) { return h ? h->last_ms : 0.f; }
 
 extern "C" lmpc_status lmpc_last_stats(const lmpc_handle* h, double* mean_n_eff, double* mean_fact,

@@ -81,6 +81,7 @@ lmpc_status launch_tile48(const LaunchCtx& c, const KBatch& kb, DevBuf* ws, cons
 struct Tuning {
   int tile_nw = 0;        // LMPC_TILE_NW: warps per QP of tile classes 1/2 (0 = measured default)
   bool debug_stats = false;  // LMPC_DEBUG_STATS: print per-solve counters to stderr
+  int host_lanes = 4;     // LMPC_HOST_LANES: slices of a large host-pointer batch in flight (copy/solve overlap); <= 1 = off
 };
 
 struct lmpc_handle {
@@ -112,5 +113,11 @@ struct lmpc_handle {
   int64_t launches = 0;
   bool pending = false;
   cudaStream_t pending_stream = nullptr;
+  // Large host-pointer batches are cut into `tune.host_lanes` slices, each with its own stream, staging
+  // buffers and workspace on THIS device (an lmpc_sharded whose shards all name h->device), so that the
+  // H2D copy of slice k+1 and the D2H copy of slice k-1 run under the solve of slice k, and the persistent
+  // kernel of slice k+1 fills the SMs as the last problems of slice k drain.  Created on first use.
+  struct lmpc_sharded* lanes = nullptr;
+  bool is_lane = false;  // a slice engine never slices again
 };
 

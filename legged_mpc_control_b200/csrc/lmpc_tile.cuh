@@ -26,6 +26,11 @@ struct TileGeom {
   __device__ static __forceinline__ int loff(int r, int c) { return frag_off(lcol(c >> 3) + (r >> 3) - (c >> 3), r, c); }
 };
 
+#ifndef LMPC_LATE_M
+#define LMPC_LATE_M 1
+#endif
+constexpr bool kLateM = LMPC_LATE_M != 0;
+
 // One tile column of the factorization with a compile-time tile count CNT = NT - J (static
 // accumulator indices, no predicated tensor instructions); the K loop stays rolled.
 template <int NT, int CNT, bool FROM_G>
@@ -35,11 +40,13 @@ __device__ __forceinline__ bool gm_column(const double2* Mf, double2* Lf, double
   if (J >= nte) return false;  // identity padding beyond the problem's own tile count: never read back
   double2* colL = Lf + 32 * G::lcol(J);              // tile (J + i, J) at colL[32 i]
   const double2* colM = Mf + 32 * (J * NT + J);      // tile (J + i, J) at colM[32 NT i]
-  double2 acc[CNT];
+  // FROM_G: the tiles of M come from L2 (~400 cycles).  They are requested here and SUBTRACTED after the K loop,
+  // so the latency runs under the trailing updates instead of in front of them.
+  double2 acc[CNT], mv[CNT];
 #pragma unroll
   for (int i = 0; i < CNT; ++i) {
-    const double2 v = FROM_G ? __ldcg(colM + 32 * NT * i) : colL[32 * i];
-    acc[i] = make_double2(-v.x, -v.y);
+    mv[i] = FROM_G ? __ldcg(colM + 32 * NT * i) : colL[32 * i];
+    acc[i] = kLateM && FROM_G ? make_double2(0.0, 0.0) : make_double2(-mv[i].x, -mv[i].y);
   }
   if (J > 0) {
     const double2* p = Lf + 32 * J;  // tile (J, 0); column K + 1 starts NT - K - 1 tiles further
@@ -51,6 +58,10 @@ __device__ __forceinline__ bool gm_column(const double2* Mf, double2* Lf, double
       for (int i = 1; i < CNT; ++i) dmma_xyt(acc[i], p[32 * i], bj);
       p += 32 * (NT - K - 1);
     }
+  }
+  if (kLateM && FROM_G) {
+#pragma unroll
+    for (int i = 0; i < CNT; ++i) { acc[i].x -= mv[i].x; acc[i].y -= mv[i].y; }
   }
   const double2 li = wm_diag8u(-acc[0].x, -acc[0].y, xb);
   colL[0] = li;
@@ -102,22 +113,41 @@ __device__ __forceinline__ bool gm_column_mw(const double2* Mf, double2* Lf, dou
   constexpr int CW = CNT > W ? (CNT - W + NW - 1) / NW : 0;  // tiles of this column owned by warp W
   double2* colL = Lf + 32 * G::lcol(J);
   const double2* colM = Mf + 32 * (J * NT + J);
-  double2 acc[CW > 0 ? CW : 1];
+  double2 acc[CW > 0 ? CW : 1], mv[CW > 0 ? CW : 1];  // (late subtraction of M: see gm_column)
 #pragma unroll
   for (int m = 0; m < CW; ++m) {
     const int i = W + NW * m;
-    const double2 v = FROM_G ? __ldcg(colM + 32 * NT * i) : colL[32 * i];
-    acc[m] = make_double2(-v.x, -v.y);
+    mv[m] = FROM_G ? __ldcg(colM + 32 * NT * i) : colL[32 * i];
+    acc[m] = kLateM && FROM_G ? make_double2(0.0, 0.0) : make_double2(-mv[m].x, -mv[m].y);
   }
   if (J > 0 && CW > 0) {
     const double2* p = Lf + 32 * J;
+    if (kLateM && CW == 1) {
+      // a single tile per warp (the late, narrow columns): the two k-chunks of every product run as separate
+      // accumulation chains, which halves the dependent DMMA chain (26 instead of 52 cycles per K)
+      double2 acb = make_double2(0.0, 0.0);
 #pragma unroll 1
-    for (int K = 0; K < J; ++K) {  // acc[m] += L_{J+i,K} L_{J,K}'
-      const double2 bj = p[0];
+      for (int K = 0; K < J; ++K) {
+        const double2 bj = p[0];
+        const double2 a = p[32 * W];
+        dmma(acc[0], a.x, bj.x);
+        dmma(acb, a.y, bj.y);
+        p += 32 * (NT - K - 1);
+      }
+      acc[0].x += acb.x; acc[0].y += acb.y;
+    } else {
+#pragma unroll 1
+      for (int K = 0; K < J; ++K) {  // acc[m] += L_{J+i,K} L_{J,K}'
+        const double2 bj = p[0];
 #pragma unroll
-      for (int m = 0; m < CW; ++m) dmma_xyt(acc[m], p[32 * (W + NW * m)], bj);
-      p += 32 * (NT - K - 1);
+        for (int m = 0; m < CW; ++m) dmma_xyt(acc[m], p[32 * (W + NW * m)], bj);
+        p += 32 * (NT - K - 1);
+      }
     }
+  }
+  if (kLateM && FROM_G) {
+#pragma unroll
+    for (int m = 0; m < CW; ++m) { acc[m].x -= mv[m].x; acc[m].y -= mv[m].y; }
   }
   bool bad = false;
   if (W == 0) {
