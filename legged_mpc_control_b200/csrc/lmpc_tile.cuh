@@ -46,7 +46,7 @@ __device__ __forceinline__ bool gm_column(const double2* Mf, double2* Lf, double
 #pragma unroll
   for (int i = 0; i < CNT; ++i) {
     mv[i] = FROM_G ? __ldcg(colM + 32 * NT * i) : colL[32 * i];
-    acc[i] = kLateM && FROM_G ? make_double2(0.0, 0.0) : make_double2(-mv[i].x, -mv[i].y);
+    acc[i] = kLateM && FROM_G && NT <= 24 ? make_double2(0.0, 0.0) : make_double2(-mv[i].x, -mv[i].y);
   }
   if (J > 0) {
     const double2* p = Lf + 32 * J;  // tile (J, 0); column K + 1 starts NT - K - 1 tiles further
@@ -59,7 +59,7 @@ __device__ __forceinline__ bool gm_column(const double2* Mf, double2* Lf, double
       p += 32 * (NT - K - 1);
     }
   }
-  if (kLateM && FROM_G) {
+  if (kLateM && FROM_G && NT <= 24) {  // (no gain where the factor itself streams from L2)
 #pragma unroll
     for (int i = 0; i < CNT; ++i) { acc[i].x -= mv[i].x; acc[i].y -= mv[i].y; }
   }
@@ -118,7 +118,7 @@ __device__ __forceinline__ bool gm_column_mw(const double2* Mf, double2* Lf, dou
   for (int m = 0; m < CW; ++m) {
     const int i = W + NW * m;
     mv[m] = FROM_G ? __ldcg(colM + 32 * NT * i) : colL[32 * i];
-    acc[m] = kLateM && FROM_G ? make_double2(0.0, 0.0) : make_double2(-mv[m].x, -mv[m].y);
+    acc[m] = kLateM && FROM_G && NT <= 24 ? make_double2(0.0, 0.0) : make_double2(-mv[m].x, -mv[m].y);
   }
   if (J > 0 && CW > 0) {
     const double2* p = Lf + 32 * J;
@@ -145,7 +145,7 @@ __device__ __forceinline__ bool gm_column_mw(const double2* Mf, double2* Lf, dou
       }
     }
   }
-  if (kLateM && FROM_G) {
+  if (kLateM && FROM_G && NT <= 24) {  // (no gain where the factor itself streams from L2)
 #pragma unroll
     for (int m = 0; m < CW; ++m) { acc[m].x -= mv[m].x; acc[m].y -= mv[m].y; }
   }
