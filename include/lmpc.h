@@ -162,7 +162,12 @@ lmpc_status lmpc_create(const lmpc_params* params, int32_t max_batch, int32_t de
 /* Replaces calc_mpc_reference + update_cons_matrix + compute_grfs (ConvexMpc.cpp:70-72) for
  * `batch` independent robots.  Blocking.  Returns LMPC_ERR_NOT_CONVERGED if any problem failed
  * (its grf is zero, as the reference returns zeros on NaN); outputs are valid either way, and
- * lmpc_last_not_converged gives the count. */
+ * lmpc_last_not_converged gives the count.
+ * Host pointers, large batch (>= 2048 problems per slice, warm start off): the batch is cut into
+ * LMPC_HOST_LANES (environment, read at lmpc_create; default 4, <= 1 = off) contiguous slices with a
+ * stream, staging buffers and workspace each on the handle's device, so the copies of one slice run
+ * under the solve of its neighbour; answers are identical to the one-shot call.  Page-locked host
+ * arrays (lmpc_alloc_pinned) are what makes those copies asynchronous. */
 lmpc_status lmpc_solve(lmpc_handle* h, int32_t batch, const lmpc_batch_in* in,
                        const lmpc_batch_out* out);
 
