@@ -105,18 +105,36 @@ static __device__ __noinline__ bool gm_factor(const double* Mg, double* Ls, doub
 // per column (inverse of the diagonal tile published; column final).  W is a template parameter so
 // that accumulator indices stay static; a helper warp whose share of a late column is empty only
 // passes the barriers.  Everything else of the solve stays on warp 0.
+// Tile ownership inside a column.  Round-robin from the diagonal down (tile i -> warp i % NW) leaves warp 0 with
+// its share of the trailing update IN FRONT of the serial diagonal tile; with kDiagWarp (classes whose factor is
+// in shared memory) warp 0 owns ONLY the diagonal tile — its chain is one split-accumulator product row plus
+// wm_diag8 — and the sub-diagonal tiles go round-robin over warps 1 .. NW-1, whose updates run beside it.
+#ifndef LMPC_DIAG_WARP
+#define LMPC_DIAG_WARP 1
+#endif
+template <int NT, int NW>
+__host__ __device__ constexpr bool diag_warp() { return LMPC_DIAG_WARP != 0 && NW >= 2 && NT <= 24; }
+template <int NT, int NW, int W>
+__host__ __device__ constexpr int mw_tile(int m) {  // m-th tile (offset from the diagonal) of warp W
+  return diag_warp<NT, NW>() ? (W == 0 ? 0 : W + (NW - 1) * m) : W + NW * m;
+}
+template <int NT, int NW, int W>
+__host__ __device__ constexpr int mw_count(int CNT) {  // tiles of a CNT-tile column owned by warp W
+  return diag_warp<NT, NW>() ? (W == 0 ? 1 : (CNT > W ? (CNT - W + NW - 2) / (NW - 1) : 0))
+                             : (CNT > W ? (CNT - W + NW - 1) / NW : 0);
+}
 template <int NT, int CNT, bool FROM_G, int NW, int W>
 __device__ __forceinline__ bool gm_column_mw(const double2* Mf, double2* Lf, double* xb, int nte) {
   using G = TileGeom<NT>;
   constexpr int J = NT - CNT;
   if (J >= nte) return false;  // CTA-uniform: every warp skips the padded columns and their barriers
-  constexpr int CW = CNT > W ? (CNT - W + NW - 1) / NW : 0;  // tiles of this column owned by warp W
+  constexpr int CW = mw_count<NT, NW, W>(CNT);  // tiles of this column owned by warp W
   double2* colL = Lf + 32 * G::lcol(J);
   const double2* colM = Mf + 32 * (J * NT + J);
   double2 acc[CW > 0 ? CW : 1], mv[CW > 0 ? CW : 1];  // (late subtraction of M: see gm_column)
 #pragma unroll
   for (int m = 0; m < CW; ++m) {
-    const int i = W + NW * m;
+    const int i = mw_tile<NT, NW, W>(m);
     mv[m] = FROM_G ? __ldcg(colM + 32 * NT * i) : colL[32 * i];
     acc[m] = kLateM && FROM_G && NT <= 24 ? make_double2(0.0, 0.0) : make_double2(-mv[m].x, -mv[m].y);
   }
@@ -129,7 +147,7 @@ __device__ __forceinline__ bool gm_column_mw(const double2* Mf, double2* Lf, dou
 #pragma unroll 1
       for (int K = 0; K < J; ++K) {
         const double2 bj = p[0];
-        const double2 a = p[32 * W];
+        const double2 a = p[32 * mw_tile<NT, NW, W>(0)];
         dmma(acc[0], a.x, bj.x);
         dmma(acb, a.y, bj.y);
         p += 32 * (NT - K - 1);
@@ -140,7 +158,7 @@ __device__ __forceinline__ bool gm_column_mw(const double2* Mf, double2* Lf, dou
       for (int K = 0; K < J; ++K) {  // acc[m] += L_{J+i,K} L_{J,K}'
         const double2 bj = p[0];
 #pragma unroll
-        for (int m = 0; m < CW; ++m) dmma_xyt(acc[m], p[32 * (W + NW * m)], bj);
+        for (int m = 0; m < CW; ++m) dmma_xyt(acc[m], p[32 * mw_tile<NT, NW, W>(m)], bj);
         p += 32 * (NT - K - 1);
       }
     }
@@ -163,7 +181,7 @@ __device__ __forceinline__ bool gm_column_mw(const double2* Mf, double2* Lf, dou
     for (int m = (W == 0 ? 1 : 0); m < CW; ++m) {
       double2 x = make_double2(0.0, 0.0);
       dmma_xyt(x, acc[m], nli);
-      colL[32 * (W + NW * m)] = x;
+      colL[32 * mw_tile<NT, NW, W>(m)] = x;
     }
   }
   __syncthreads();  // column J final
