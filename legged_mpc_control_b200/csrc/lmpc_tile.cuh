@@ -114,14 +114,32 @@ static __device__ __noinline__ bool gm_factor(const double* Mg, double* Ls, doub
 #endif
 template <int NT, int NW>
 __host__ __device__ constexpr bool diag_warp() { return LMPC_DIAG_WARP != 0 && NW >= 2 && NT <= 24; }
+// With eight warps two warps share a scheduler (warp w runs on scheduler w % 4) and the FP64 tensor pipe issues one
+// DMMA per 16 cycles per scheduler, in order: the dependent DMMAs of wm_diag8 on warp 0 queue behind the update
+// stream of warp 4.  LMPC_DIAG_ALONE leaves warp 4 out of the factorization, so the diagonal warp has its pipe alone.
+#ifndef LMPC_DIAG_ALONE
+#define LMPC_DIAG_ALONE 1
+#endif
+template <int NT, int NW>
+__host__ __device__ constexpr bool diag_alone() { return LMPC_DIAG_ALONE != 0 && diag_warp<NT, NW>() && NW == 8; }
+template <int NT, int NW>
+__host__ __device__ constexpr int mw_workers() { return diag_alone<NT, NW>() ? 6 : NW - 1; }  // warps that share the sub-diagonal tiles
+template <int NT, int NW, int W>
+__host__ __device__ constexpr int mw_worker() {  // index of warp W among those workers, -1: none
+  return diag_alone<NT, NW>() ? (W == 0 || W == 4 ? -1 : (W < 4 ? W - 1 : W - 2)) : W - 1;
+}
 template <int NT, int NW, int W>
 __host__ __device__ constexpr int mw_tile(int m) {  // m-th tile (offset from the diagonal) of warp W
-  return diag_warp<NT, NW>() ? (W == 0 ? 0 : W + (NW - 1) * m) : W + NW * m;
+  return diag_warp<NT, NW>() ? (W == 0 ? 0 : 1 + mw_worker<NT, NW, W>() + mw_workers<NT, NW>() * m) : W + NW * m;
 }
 template <int NT, int NW, int W>
 __host__ __device__ constexpr int mw_count(int CNT) {  // tiles of a CNT-tile column owned by warp W
-  return diag_warp<NT, NW>() ? (W == 0 ? 1 : (CNT > W ? (CNT - W + NW - 2) / (NW - 1) : 0))
-                             : (CNT > W ? (CNT - W + NW - 1) / NW : 0);
+  return diag_warp<NT, NW>()
+             ? (W == 0 ? 1
+                       : (mw_worker<NT, NW, W>() >= 0 && CNT - 1 > mw_worker<NT, NW, W>()
+                              ? (CNT - 1 - mw_worker<NT, NW, W>() + mw_workers<NT, NW>() - 1) / mw_workers<NT, NW>()
+                              : 0))
+             : (CNT > W ? (CNT - W + NW - 1) / NW : 0);
 }
 template <int NT, int CNT, bool FROM_G, int NW, int W>
 __device__ __forceinline__ bool gm_column_mw(const double2* Mf, double2* Lf, double* xb, int nte) {
