@@ -295,21 +295,24 @@ __device__ __forceinline__ void gm_solve_impl(const double* Ls, double* x, const
 #pragma unroll 1
   for (int J = nte - 1; J >= 0; --J) {
     const double* ct = Ls + 64 * G::lcol(J) + 16 * t + g;  // transposed reads of column J: tile i at ct[64 i], ct[64 i + 8]
+    const double* cs = Ls + 64 * G::lcol(J);               // ... and the two-way-conflict form for the off-diagonal tiles
     double pa[4] = {0.0, 0.0, 0.0, 0.0}, pb[4] = {0.0, 0.0, 0.0, 0.0};
     int i = 1;
     for (; NT > 24 && i + 4 <= nte - J; i += 4) {
 #pragma unroll
       for (int u = 0; u < 4; ++u) {
-        const double2 xi = xt[4 * (J + i + u)];
-        pa[u] = fma(ct[64 * (i + u)], xi.x, pa[u]);
-        pb[u] = fma(ct[64 * (i + u) + 8], xi.y, pb[u]);
+        const double2 xi = vec_ld_tr<kTransS && NT <= 24>(x, J + i + u, t);
+        const double2 c = tile_ld_tr<kTransS && NT <= 24>(cs + 64 * (i + u), g, t);
+        pa[u] = fma(c.x, xi.x, pa[u]);
+        pb[u] = fma(c.y, xi.y, pb[u]);
       }
     }
 #pragma unroll 4
     for (; i < nte - J; ++i) {
-      const double2 xi = xt[4 * (J + i)];
-      pa[0] = fma(ct[64 * i], xi.x, pa[0]);
-      pb[0] = fma(ct[64 * i + 8], xi.y, pb[0]);
+      const double2 xi = vec_ld_tr<kTransS && NT <= 24>(x, J + i, t);
+      const double2 c = tile_ld_tr<kTransS && NT <= 24>(cs + 64 * i, g, t);
+      pa[0] = fma(c.x, xi.x, pa[0]);
+      pb[0] = fma(c.y, xi.y, pb[0]);
     }
     const double p0 = (pa[0] + pa[1]) + (pa[2] + pa[3]), p1 = (pb[0] + pb[1]) + (pb[2] + pb[3]);
     double2 r = xt[4 * J];
@@ -400,8 +403,8 @@ __device__ __forceinline__ void gm_solve_mw_impl(const double* Ls, double* x, do
       for (int u = 0; u < BS - 1; ++u) {
         const int K = d0 + u;
         if (K < J) {
-          const double2 c = tile_ld_t(Ls + 64 * (G::lcol(K) + J - K), g, t);
-          const double2 r = xt[4 * K];
+          const double2 c = tile_ld_tr<kTransS && NT <= 24>(Ls + 64 * (G::lcol(K) + J - K), g, t);
+          const double2 r = vec_ld_tr<kTransS && NT <= 24>(x, K, t);
           p0 = fma(c.x, r.x, p0);
           p1 = fma(c.y, r.y, p1);
         }
@@ -433,8 +436,8 @@ __device__ __forceinline__ void gm_solve_mw_impl(const double* Ls, double* x, do
   for (int d0 = dlast; d0 >= 0; d0 -= BS) {
     const int d1 = d0 + BS < nte ? d0 + BS : nte;
     for (int J = d0 + w; J < d1; J += NW) {  // x_J = inv(L_bb)'[J, :] y   (column J of the block inverse: direct slots)
-      const double2 c = tile_ld_t(Ls + 64 * G::lcol(J), g, t);
-      const double2 yj = yt[4 * J];
+      const double2 c = tile_ld_tr<kTransS && NT <= 24>(Ls + 64 * G::lcol(J), g, t);
+      const double2 yj = vec_ld_tr<kTransS && NT <= 24>(tt, J, t);
       double p0 = c.x * yj.x, p1 = c.y * yj.y;
 #pragma unroll
       for (int u = 1; u < BS; ++u) {
@@ -450,15 +453,16 @@ __device__ __forceinline__ void gm_solve_mw_impl(const double* Ls, double* x, do
     }
     __syncthreads();
     for (int J = w; J < d0; J += NW) {  // y_J -= sum_{I in block} L_IJ' x_I
-      const double* ct = Ls + 64 * G::lcol(J) + 16 * t + g;
+      const double* cs = Ls + 64 * G::lcol(J);
       double p0 = 0.0, p1 = 0.0;
 #pragma unroll
       for (int u = 0; u < BS; ++u) {
         const int I = d0 + u;
         if (I < d1) {
-          const double2 xi = xt[4 * I];
-          p0 = fma(ct[64 * (I - J)], xi.x, p0);
-          p1 = fma(ct[64 * (I - J) + 8], xi.y, p1);
+          const double2 xi = vec_ld_tr<kTransS && NT <= 24>(x, I, t);
+          const double2 c = tile_ld_tr<kTransS && NT <= 24>(cs + 64 * (I - J), g, t);
+          p0 = fma(c.x, xi.x, p0);
+          p1 = fma(c.y, xi.y, p1);
         }
       }
       const double2 s = quad_reduce_t(p0 + p1);

@@ -151,6 +151,29 @@ __device__ __forceinline__ double2 tile_ld_t(const double* tile, int g, int t) {
   return make_double2(p[0], p[8]);
 }
 
+// The same transposed product with HALF the bank conflicts.  A tile row is 64 bytes, so rows of equal parity sit in
+// the same 16 banks: tile_ld_t (rows 2t and 2t+1 of column g, one LDS.64 each) makes the four lanes of a quad hit the
+// same banks — a four-way conflict, 8 wavefronts per load.  Reading rows t and t+4 instead puts two parities into
+// every load (two-way, 4 wavefronts); the lane then multiplies with the vector elements 8K+t and 8K+t+4 and the quad
+// sum over t is the same column-g result.  For vectors that live in shared memory.
+#ifndef LMPC_TRANS_S
+#define LMPC_TRANS_S 1
+#endif
+constexpr bool kTransS = LMPC_TRANS_S != 0;
+// S (the factor is in shared memory): returns {T[t][g], T[t+4][g]}; else {T[2t][g], T[2t+1][g]} (a factor in the
+// global slot has no banks, and the rows-t/t+4 pattern measured 5 % slower on class 36)
+template <bool S>
+__device__ __forceinline__ double2 tile_ld_tr(const double* tile, int g, int t) {
+  const double* p = tile + (S ? 8 * t : 16 * t) + g;
+  return make_double2(p[0], p[S ? 32 : 8]);
+}
+// the matching pair of block K of the vector x: {x[8K+t], x[8K+t+4]} or {x[8K+2t], x[8K+2t+1]}
+template <bool S>
+__device__ __forceinline__ double2 vec_ld_tr(const double* x, int K, int t) {
+  if (S) return make_double2(x[8 * K + t], x[8 * K + t + 4]);
+  return *reinterpret_cast<const double2*>(x + 8 * K + 2 * t);
+}
+
 // Factor the SPD 8x8 tile A (C-layout, full symmetric) and return G = inv(L) (lower triangular,
 // C-layout; G A G' = I).  Elimination by 2x2 BLOCK pivots (rows 2s, 2s+1 at step s = 0, 1, 2):
 //   rows g > 2s+1:  row_g -= [A[g][2s] A[g][2s+1]] inv(P_s) [row_2s; row_2s+1],   P_s = A[2s..2s+1][2s..2s+1],
