@@ -343,7 +343,10 @@ static __device__ __noinline__ void gm_solve(const double* Ls, double* x, int nt
 // diagonal slots still hold inv(L_II); a slot (I, K), I > K, INSIDE a diagonal block holds the
 // TRANSPOSE of tile (I, K) of inv(L_bb) (that is what the DMMA product X * Y' delivers without a
 // layout change: V_KI = -(sum_{k=K}^{I-1} V_Kk L_Ik') inv(L_II)',  V_KK = inv(L_KK)').
-constexpr int kTileSolveBS = 4;
+#ifndef LMPC_TILE_BS
+#define LMPC_TILE_BS 4
+#endif
+constexpr int kTileSolveBS = LMPC_TILE_BS;
 
 template <int NT, int BS>
 __device__ __forceinline__ void gm_block_inverse(double* Ls, int d0, int d1) {
