@@ -96,6 +96,8 @@ static void fill_kparams(const lmpc_params& p, KParams* k) {
   // the interior point is only the fallback when its repair rounds do not verify.
   k->step_frac = 0.999; k->sigma_pow = 3;  // swept on the headline workload (tools/gpu_sweep2.sh): flat within 1 %, 0.999 leaves the fewest interior-point-only answers
   if (const char* e = getenv("LMPC_STEP_FRAC")) k->step_frac = atof(e);
+  k->z0_scale = 1e-4;  // swept on every workload (tools/gpu_r2_z0.sh, profiles/r02_v12_z0_sweep.txt): 1 -> 1e-4 saves 2.5-3 factorizations per cold solve
+  if (const char* e = getenv("LMPC_Z0_SCALE")) k->z0_scale = atof(e);
   if (const char* e = getenv("LMPC_SIGMA_POW")) k->sigma_pow = atoi(e);
   k->dual_rel = 1e-11;  // 1e-9 let multipliers of -1e-10 pass: amplified by cond(H) ~ 1e7 that moved late-horizon forces by 6e-6 relative (tests/test_gpu_parity_fullsize.py)
   if (const char* e = getenv("LMPC_DUAL_REL")) k->dual_rel = atof(e);
@@ -121,7 +123,8 @@ static lmpc_status create_resources(lmpc_handle* h) {
   CK(cudaEventCreate(&h->ev0));
   CK(cudaEventCreate(&h->ev1));
   CK(h->d_stats.ensure(sizeof(KStats)));
-  CK(h->d_counter.ensure(2 * lmpc::kCtrCount * sizeof(int)));  // work counters, class sizes
+  CK(h->d_counter.ensure(4 * lmpc::kCtrCount * sizeof(int)));  // work counters, class sizes, and the same two for the retry launches
+  CK(h->d_retry.ensure(lmpc::kNumClasses * (size_t)h->max_batch * sizeof(int)));
   CK(h->d_order.ensure(lmpc::kNumClasses * (size_t)h->max_batch * sizeof(int)));
   return LMPC_OK;
 }
@@ -150,6 +153,8 @@ extern "C" lmpc_status lmpc_create(const lmpc_params* params, int32_t max_batch,
   lmpc_handle* h = new lmpc_handle();
   h->params = *params;
   fill_kparams(*params, &h->kp);
+  h->kp_retry = h->kp;
+  h->kp_retry.z0_scale = 1.0;
   h->device = device;
   h->max_batch = max_batch;
   h->num_sms = prop.multiProcessorCount;
@@ -184,7 +189,7 @@ extern "C" void lmpc_destroy(lmpc_handle* h) {
   if (h->stream) cudaStreamSynchronize(h->stream);
   DevBuf* bufs[] = {&h->d_x0, &h->d_rot, &h->d_foot, &h->d_cmd, &h->d_contact, &h->d_q, &h->d_r, &h->d_mu,
                     &h->d_fz, &h->d_mass, &h->d_inertia, &h->d_grf, &h->d_status, &h->d_iters, &h->d_active,
-                    &h->d_U, &h->d_stats, &h->d_counter, &h->d_ws, &h->d_wsA, &h->d_wsT1, &h->d_wsT2, &h->d_wsT3, &h->d_order, &h->d_warm,
+                    &h->d_U, &h->d_stats, &h->d_counter, &h->d_ws, &h->d_wsA, &h->d_wsT1, &h->d_wsT2, &h->d_wsT3, &h->d_order, &h->d_warm, &h->d_retry,
                     &h->d_pin, &h->d_pout, &h->d_rx, &h->d_rfw, &h->d_rph, &h->d_rgait, &h->d_rspeed, &h->d_rtot, &h->d_xlog, &h->d_glog, &h->d_rfsm, &h->d_aux};
   for (DevBuf* b : bufs) b->release();
   if (h->ev0) cudaEventDestroy(h->ev0);
@@ -202,42 +207,65 @@ extern "C" void lmpc_destroy(lmpc_handle* h) {
 // no host synchronisation.  A class is launched only if the horizon can produce it (n <= 12 H).
 // class_mask: bit c set = size class c may be non-empty (host-pointer calls know the contact rows and skip
 // the launches of the classes no problem falls into; device-pointer calls pass ~0u).
-static lmpc_status launch_solve(lmpc_handle* h, KBatch kb, cudaStream_t s, unsigned class_mask = ~0u) {
+// mode 0: both passes enqueued (any batch, no host synchronisation); 1: the first pass only, failures are counted
+// (the packed small-batch path looks at the count on the host and calls again with mode 2); 2: one pass from the
+// conservative start.
+static lmpc_status launch_solve(lmpc_handle* h, KBatch kb, cudaStream_t s, unsigned class_mask = ~0u, int mode = 0) {
   const int H = h->kp.H;
   kb.warm = h->warm_enabled ? (uint8_t*)h->d_warm.p : nullptr;
   kb.warm_shift = h->warm_shift;
   KStats* dstats = (KStats*)h->d_stats.p;
-  int* ctr = (int*)h->d_counter.p;  // [c] work counters, [kCtrCount + c] class sizes
+  int* ctr = (int*)h->d_counter.p;  // [c] work counters, [kCtrCount + c] class sizes, then the retry launches' pair
   int* cnt = ctr + lmpc::kCtrCount;
+  int* rctr = ctr + 2 * lmpc::kCtrCount;
+  int* rcnt = ctr + 3 * lmpc::kCtrCount;
   int* order = (int*)h->d_order.p;  // class c at order + c * max_batch
+  int* rlist = (int*)h->d_retry.p;  // same layout: what class c's first launch could not solve
   const size_t stride = (size_t)h->max_batch;
   CK(cudaMemsetAsync(dstats, 0, sizeof(KStats), s));
-  CK(cudaMemsetAsync(ctr, 0, 2 * lmpc::kCtrCount * sizeof(int), s));
+  CK(cudaMemsetAsync(ctr, 0, 4 * lmpc::kCtrCount * sizeof(int), s));
   CK(cudaEventRecord(h->ev0, s));
   lmpc::classify_kernel<<<(kb.B + 255) / 256, 256, 0, s>>>(kb.contact, H, kb.B, dstats, order, (int)stride, cnt);
   h->launches++;
-  const lmpc::LaunchCtx c{h->device, &h->kp, dstats, h->num_sms, s, &h->launches};
   const int nmax = 12 * H;  // largest reduced dimension this horizon can produce
-  lmpc_status st = LMPC_OK;
-  if (class_mask & 1u)
-    st = h->kp.class0_on_tiles ? lmpc::launch_tile8(c, kb, &h->d_wsA, order, cnt + 0, ctr + 0, 1)
-                               : lmpc::launch_warp_class(c, kb, &h->d_wsA, order, cnt + 0, ctr + 0);
-  if (st != LMPC_OK) return st;
-  if (nmax > lmpc::kWarpNMax && (class_mask & 2u)) {
-    st = lmpc::launch_tile15(c, kb, &h->d_wsT1, order + stride, cnt + 1, ctr + 1, h->tune.tile_nw);
+  // Pass 0 solves every class from the small initial complementarity (kp.z0_scale); the few problems it cannot
+  // solve are collected per class and pass 1 runs the same kernels over those lists with the conservative start.
+  // Both passes are enqueued back to back (the list lengths live on the device): no host synchronisation.
+  const int passes = (mode == 0 && h->kp.z0_scale < 1.0) ? 2 : 1;
+  for (int pass = 0; pass < passes; ++pass) {
+    const bool first = pass == 0;
+    const lmpc::LaunchCtx c{h->device, (first && mode != 2) ? &h->kp : &h->kp_retry, dstats, h->num_sms, s, &h->launches};
+    const int* lst = first ? order : rlist;
+    const int* len = first ? cnt : rcnt;
+    int* wrk = first ? ctr : rctr;
+    auto with_retry = [&](int cls) {  // the batch as class `cls` sees it in this pass
+      KBatch k = kb;
+      k.retry_list = (first && passes == 2) ? rlist + (size_t)cls * stride : nullptr;
+      k.retry_count = (first && passes == 2) ? rcnt + cls : nullptr;
+      if (!first && k.B > 64) k.B = 64;  // (B only caps the grid) a handful of problems: a small grid walks the list
+      return k;
+    };
+    lmpc_status st = LMPC_OK;
+    if (class_mask & 1u)
+      st = h->kp.class0_on_tiles ? lmpc::launch_tile8(c, with_retry(0), &h->d_wsA, lst, len + 0, wrk + 0, 1)
+                                 : lmpc::launch_warp_class(c, with_retry(0), &h->d_wsA, lst, len + 0, wrk + 0);
     if (st != LMPC_OK) return st;
-  }
-  if (nmax > 8 * lmpc::kTileA && (class_mask & 4u)) {
-    st = lmpc::launch_tile24(c, kb, &h->d_wsT2, order + 2 * stride, cnt + 2, ctr + 2, h->tune.tile_nw);
-    if (st != LMPC_OK) return st;
-  }
-  if (nmax > 8 * lmpc::kTileB && (class_mask & 16u)) {  // class 4 (192 < n <= 288)
-    st = lmpc::launch_tile36(c, kb, &h->d_wsT3, order + 4 * stride, cnt + 4, ctr + 4, 0);
-    if (st != LMPC_OK) return st;
-  }
-  if (nmax > 8 * lmpc::kTileD && (class_mask & 8u)) {  // class 3 (n > 288): only horizons above 24 reach it
-    st = lmpc::launch_tile48(c, kb, &h->d_ws, order + 3 * stride, cnt + 3, ctr + 3, 0);
-    if (st != LMPC_OK) return st;
+    if (nmax > lmpc::kWarpNMax && (class_mask & 2u)) {
+      st = lmpc::launch_tile15(c, with_retry(1), &h->d_wsT1, lst + stride, len + 1, wrk + 1, h->tune.tile_nw);
+      if (st != LMPC_OK) return st;
+    }
+    if (nmax > 8 * lmpc::kTileA && (class_mask & 4u)) {
+      st = lmpc::launch_tile24(c, with_retry(2), &h->d_wsT2, lst + 2 * stride, len + 2, wrk + 2, h->tune.tile_nw);
+      if (st != LMPC_OK) return st;
+    }
+    if (nmax > 8 * lmpc::kTileB && (class_mask & 16u)) {  // class 4 (192 < n <= 288)
+      st = lmpc::launch_tile36(c, with_retry(4), &h->d_wsT3, lst + 4 * stride, len + 4, wrk + 4, 0);
+      if (st != LMPC_OK) return st;
+    }
+    if (nmax > 8 * lmpc::kTileD && (class_mask & 8u)) {  // class 3 (n > 288): only horizons above 24 reach it
+      st = lmpc::launch_tile48(c, with_retry(3), &h->d_ws, lst + 3 * stride, len + 3, wrk + 3, 0);
+      if (st != LMPC_OK) return st;
+    }
   }
   CK(cudaEventRecord(h->ev1, s));
   return LMPC_OK;
@@ -356,12 +384,19 @@ extern "C" lmpc_status lmpc_solve(lmpc_handle* h, int32_t batch, const lmpc_batc
     }
     void* saved = h->d_stats.p;  // the statistics block rides at the head of the packed output
     h->d_stats.p = dout;
-    st = launch_solve(h, kb, s, mask);
-    h->d_stats.p = saved;
-    if (st != LMPC_OK) return st;
+    st = launch_solve(h, kb, s, mask, 1);
+    if (st != LMPC_OK) { h->d_stats.p = saved; return st; }
     CK(cudaMemcpyAsync(h->h_pout, dout, out_bytes, cudaMemcpyDeviceToHost, s));
     CK(cudaStreamSynchronize(s));
     memcpy(&h->last_stats, h->h_pout, sizeof(KStats));
+    if (h->last_stats.not_ok > 0 && h->kp.z0_scale < 1.0) {  // rare: once more from the conservative interior-point start
+      st = launch_solve(h, kb, s, mask, 2);
+      if (st != LMPC_OK) { h->d_stats.p = saved; return st; }
+      CK(cudaMemcpyAsync(h->h_pout, dout, out_bytes, cudaMemcpyDeviceToHost, s));
+      CK(cudaStreamSynchronize(s));
+      memcpy(&h->last_stats, h->h_pout, sizeof(KStats));
+    }
+    h->d_stats.p = saved;
     memcpy(out->grf, h->h_pout + p_grf, nb * 96);
     if (out->status) memcpy(out->status, h->h_pout + p_st, nb * 4);
     if (out->iters) memcpy(out->iters, h->h_pout + p_it, nb * 4);

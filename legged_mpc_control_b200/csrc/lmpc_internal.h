@@ -44,7 +44,7 @@ struct DevBuf {
 //   4: 193 <= n <= 288    36 x 36 tiles, factor in the global slot (solve_tile_kernel<36>)
 //   3: n > 288            48 x 48 tiles, factor in the global slot (solve_tile_kernel<48>)
 constexpr int kNumClasses = 5;
-constexpr int kCtrCount = 8;   // counter block: work counters at [c], class sizes at [kCtrCount + c]
+constexpr int kCtrCount = 8;   // counter block: work counters at [c], class sizes at [kCtrCount + c]; retry launches: work counters at [2 kCtrCount + c], list lengths at [3 kCtrCount + c]
 constexpr int kWarpNMax = 63;  // 3 * WNBMAX
 constexpr int kTileA = 15, kTileB = 24, kTileC = 48;  // 8 x 48 = 384 = 12 x LMPC_MAX_HORIZON
 constexpr int kTileD = 36;     // class 4: 192 < n <= 288 (crawl at H = 30, stand at H = 20)
@@ -97,6 +97,8 @@ struct lmpc_handle {
   lmpc::DevBuf d_x0, d_rot, d_foot, d_cmd, d_contact, d_q, d_r, d_mu, d_fz, d_mass, d_inertia;
   lmpc::DevBuf d_grf, d_status, d_iters, d_active, d_U;
   lmpc::DevBuf d_stats, d_counter, d_ws, d_wsA, d_wsT1, d_wsT2, d_wsT3, d_order, d_warm;
+  lmpc::DevBuf d_retry;     // per size class: the problems the first launch handed to the retry launch (KBatch::retry_list)
+  lmpc::KParams kp_retry;   // kp with the conservative interior-point start (z0_scale = 1)
   bool warm_enabled = false;
   int warm_shift = 1;
   // small-batch host path: one packed H2D and one packed D2H (a single robot's tick is latency-bound)

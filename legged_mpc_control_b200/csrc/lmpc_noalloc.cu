@@ -142,11 +142,12 @@ extern "C" lmpc_status lmpc_solve_noalloc(lmpc_handle* h, int32_t batch, const l
   kb.order = nullptr;
   kb.B = batch;
   kb.warm = nullptr; kb.warm_shift = 0;  // no warm start: its record store is a cudaMalloc'ed buffer of the handle
+  kb.retry_list = nullptr; kb.retry_count = nullptr;  // one launch, no retry list (it would be a cudaMalloc'ed buffer): ...
 
   cudaStream_t s = cuda_stream ? (cudaStream_t)cuda_stream : h->stream;
   CK(cudaMemsetAsync(scratch, 0, lmpc::kNoAllocHeader, s));  // work counter, too-large counter, statistics
   const int grid = batch < lmpc::kNoAllocSlots ? batch : lmpc::kNoAllocSlots;
-  lmpc::solve_warp_static_kernel<<<grid, 32, wp.total_bytes, s>>>(h->kp, kb, scratch);
+  lmpc::solve_warp_static_kernel<<<grid, 32, wp.total_bytes, s>>>(h->kp_retry, kb, scratch);  // ... so the conservative interior-point start
   CK(cudaGetLastError());
   h->launches++;
   if (!blocking) return LMPC_OK;

@@ -509,7 +509,7 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
         }
         const double ginf = wmax(gi);
         ssum = wsum(ssum);
-        const double zc = (ginf > 1e-6 ? ginf : 1e-6) * (ssum * inv_m);
+        const double zc = P.z0_scale * (ginf > 1e-6 ? ginf : 1e-6) * (ssum * inv_m);
         for (int b = lane; b < nb; b += 32) {
           double s[5];
           blk_slack(u + 3 * b, mu, fzm, s);
@@ -882,8 +882,13 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
       if (Bt.iters) Bt.iters[p64] = (nf & 0xffff) | (n_polish << 16);
     }
     if (status == 0 && n_ipm == 0) ws.warm_hits++;
-    ws.problems++; ws.sum_n += n; ws.sum_fact += nf; ws.sum_polish += n_polish;
-    if (status >= 2) ws.not_ok++;
+    // no answer from the small-complementarity start: hand the problem to the retry launch (conservative start),
+    // whose outputs replace the zeros written above; it is counted there
+    const bool handed = status >= 2 && Bt.retry_list != nullptr;
+    if (handed && lane == 0) Bt.retry_list[atomicAdd(Bt.retry_count, 1)] = pi;
+    if (!handed) { ws.problems++; ws.sum_n += n; }
+    ws.sum_fact += nf; ws.sum_polish += n_polish;
+    if (status >= 2 && !handed) ws.not_ok++;
     if (status == 1) ws.ipm_only++;
     const double dn = (double)n;
     ws.flops += (double)nf * (dn * dn * dn / 3.0) + (double)n_ipm * (4.0 * dn * dn + 2.0 * dn * dn) +

@@ -17,6 +17,7 @@ struct KParams {
   double rdtol0;  // relative dual-residual target of the first stage
   double fz0;     // initial fz as a fraction of fz_max (<= 0: m g / #stance legs of the step)
   double step_frac; // fraction of the step to the boundary (0.995)
+  double z0_scale;  // initial complementarity relative to |grad|_inf * mean slack (see lmpc_api.cu fill_kparams)
   double dual_rel;  // multiplier sign tolerance of the exact polish, relative to the gradient scale
   int sigma_pow;    // exponent of the Mehrotra centering rule (3)
   int try_interior; // experiment: cold problems first try the polish from all-interior faces
@@ -53,6 +54,11 @@ struct KBatch {
   // (one per step x leg, see face_encode) + 4 header bytes (byte 4H: record valid).  nullptr -> cold.
   uint8_t* warm;
   int warm_shift;        // horizon steps elapsed since the stored solve (1 when control dt == MPC dt)
+  // Problems a launch could not solve (status >= 2) are appended here instead of being counted as failures; the
+  // host enqueues a second launch of the same kernel over this list with the conservative interior-point start
+  // (KParams::z0_scale = 1).  nullptr -> this launch is final.
+  int* retry_list;
+  int* retry_count;
 };
 
 __host__ __device__ inline int warm_stride(int H) { return 4 * H + 4; }

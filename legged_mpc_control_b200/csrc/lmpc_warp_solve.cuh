@@ -399,7 +399,7 @@ static __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpSt
     }
     const double ginf = wmax(gi);
     ssum = wsum(ssum);
-    const double zc = (ginf > 1e-6 ? ginf : 1e-6) * (ssum * inv_m);
+    const double zc = P.z0_scale * (ginf > 1e-6 ? ginf : 1e-6) * (ssum * inv_m);
     if (act)
 #pragma unroll
       for (int r = 0; r < 5; ++r) zr[r] = zc * frcp(s[r]);
@@ -800,8 +800,13 @@ static __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpSt
     }
     const int nf = n_ipm + n_polish;
     if (status == 0 && n_ipm == 0) ws.warm_hits++;
-    ws.problems++; ws.sum_n += n; ws.sum_fact += nf; ws.sum_polish += n_polish;
-    if (status >= 2) ws.not_ok++;
+    // no answer from the small-complementarity start: hand the problem to the retry launch (conservative start),
+    // whose outputs replace the zeros written above; it is counted there
+    const bool handed = status >= 2 && Bt.retry_list != nullptr;
+    if (handed && lane == 0) Bt.retry_list[atomicAdd(Bt.retry_count, 1)] = pi;
+    if (!handed) { ws.problems++; ws.sum_n += n; }
+    ws.sum_fact += nf; ws.sum_polish += n_polish;
+    if (status >= 2 && !handed) ws.not_ok++;
     if (status == 1) ws.ipm_only++;
     const double dn = (double)n;
     ws.flops += (double)nf * (dn * dn * dn / 3.0) + (double)n_ipm * (4.0 * dn * dn + 2.0 * dn * dn) +

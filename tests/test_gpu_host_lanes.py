@@ -58,3 +58,38 @@ def test_small_and_warm_batches_stay_one_shot():
     _, _, l_small, _ = _solve(p, b, 4)
     _, _, l_one, _ = _solve(p, b, 1)
     assert l_small == l_one
+
+
+def test_retry_pass_from_the_conservative_start():
+    """The interior point starts from a small complementarity (KParams::z0_scale, LMPC_Z0_SCALE); what that pass
+    cannot solve is handed to a second launch with the classical start.  A start far too small to work at all must
+    therefore still return every minimiser — from the second pass."""
+    from legged_mpc_control_b200.engine import ConvexMpcEngine
+    p = presets.preset("northstar_a1")
+    b = synth.make_batch(2048, p.horizon, p.dt, 21)
+
+    def run(scale):
+        old = os.environ.get("LMPC_Z0_SCALE")
+        os.environ["LMPC_Z0_SCALE"] = scale
+        try:
+            eng = ConvexMpcEngine(p, 2048, device=0)
+        finally:
+            if old is None:
+                del os.environ["LMPC_Z0_SCALE"]
+            else:
+                os.environ["LMPC_Z0_SCALE"] = old
+        out = eng.compute_grfs(b, want_U=False)
+        st = eng.last_stats()
+        eng.close()
+        return out, st
+
+    ref, st_ref = run("1")
+    bad, st_bad = run("1e-300")
+    assert (ref["status"] <= abi.PROB_OK_IPM_ONLY).all()
+    assert (bad["status"] <= abi.PROB_OK_IPM_ONLY).all()
+    scale = np.maximum(np.abs(ref["grf"]).max(axis=1, keepdims=True), 1.0)
+    assert (np.abs(bad["grf"] - ref["grf"]) / scale).max() <= 1e-9
+    assert st_bad["mean_factorizations"] > st_ref["mean_factorizations"]   # the wasted first attempts are counted
+    dflt, _ = run("1e-4")
+    assert (dflt["status"] <= abi.PROB_OK_IPM_ONLY).all()
+    assert (np.abs(dflt["grf"] - ref["grf"]) / scale).max() <= 1e-9

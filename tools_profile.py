@@ -22,8 +22,11 @@ dev = torch.device("cuda:0")
 tin = {k: torch.from_numpy(b[k]).to(dev) for k in ("x0", "rot", "foot_pos_abs", "cmd", "contact")}
 grf = torch.zeros(B, 12, dtype=torch.float64, device=dev)
 st = torch.zeros(B, dtype=torch.int32, device=dev)
+it = torch.zeros(B, dtype=torch.int32, device=dev)
 eng = ConvexMpcEngine(p, B)
 for _ in range(reps):
-    eng.solve_device({k: v.data_ptr() for k, v in tin.items()}, {"grf": grf.data_ptr(), "status": st.data_ptr()}, B)
-print("kernel ms", eng.last_kernel_ms, "solves/s", B / eng.last_kernel_ms * 1e3, eng.last_stats(), "bad", int((st > 1).sum()))
+    eng.solve_device({k: v.data_ptr() for k, v in tin.items()}, {"grf": grf.data_ptr(), "status": st.data_ptr(), "iters": it.data_ptr()}, B)
+pol = (it >> 16).double(); fac = (it & 0xFFFF).double()
+print("kernel ms", eng.last_kernel_ms, "solves/s", B / eng.last_kernel_ms * 1e3, eng.last_stats(), "bad", int((st > 1).sum()),
+      "polish rounds mean %.3f max %d" % (float(pol.mean()), int(pol.max())), "ipm iterations mean %.3f max %d" % (float((fac - pol).mean()), int((fac - pol).max())))
 eng.close()
