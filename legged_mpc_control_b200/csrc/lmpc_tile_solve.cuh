@@ -615,7 +615,7 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
       }
       szaff = wsum(szaff);
       const double rat = szaff * frcp(sz);
-      const double smu = rat * rat * rat * mub;  // sigma * mu
+      const double smu = (P.sigma_pow == 2 ? rat * rat : (P.sigma_pow == 4 ? rat * rat * rat * rat : rat * rat * rat)) * mub;  // sigma * mu
       // corrector: rhs = -rd - C'((sigma mu - ds_aff dz_aff - s z)/s); rd keeps the rhs
       for (int b = lane; b < nb; b += 32) {
         double w2[5], ct[3];
