@@ -207,9 +207,16 @@ extern "C" void lmpc_destroy(lmpc_handle* h) {
 // no host synchronisation.  A class is launched only if the horizon can produce it (n <= 12 H).
 // class_mask: bit c set = size class c may be non-empty (host-pointer calls know the contact rows and skip
 // the launches of the classes no problem falls into; device-pointer calls pass ~0u).
-// mode 0: both passes enqueued (any batch, no host synchronisation); 1: the first pass only, failures are counted
-// (the packed small-batch path looks at the count on the host and calls again with mode 2); 2: one pass from the
-// conservative start.
+// mode 0: both passes enqueued back to back (no host synchronisation: asynchronous calls, the closed loop);
+//      1: the first pass only, failures are counted (the packed small-batch path looks at the count on the host and
+//         calls again with mode 2);
+//      2: one pass from the conservative start (also what a warm-started engine uses: its interior point only runs
+//         for the few problems whose stored faces do not verify);
+//      3: the first pass, failures handed to the per-class lists (KStats::handed says whether there are any);
+//      4: the retry pass over those lists — no reset, no classification: continues the launch of mode 3.
+// Blocking calls use 3, read the statistics, and enqueue 4 only if something was handed over: the retry launches
+// are empty almost always, and an empty launch behind the persistent grids still cost ~75 us each
+// (warm-started 65 536-problem batch: 4.20 -> 4.35 ms with two of them).
 static lmpc_status launch_solve(lmpc_handle* h, KBatch kb, cudaStream_t s, unsigned class_mask = ~0u, int mode = 0) {
   const int H = h->kp.H;
   kb.warm = h->warm_enabled ? (uint8_t*)h->d_warm.p : nullptr;
@@ -222,53 +229,76 @@ static lmpc_status launch_solve(lmpc_handle* h, KBatch kb, cudaStream_t s, unsig
   int* order = (int*)h->d_order.p;  // class c at order + c * max_batch
   int* rlist = (int*)h->d_retry.p;  // same layout: what class c's first launch could not solve
   const size_t stride = (size_t)h->max_batch;
-  CK(cudaMemsetAsync(dstats, 0, sizeof(KStats), s));
-  CK(cudaMemsetAsync(ctr, 0, 4 * lmpc::kCtrCount * sizeof(int), s));
-  CK(cudaEventRecord(h->ev0, s));
-  lmpc::classify_kernel<<<(kb.B + 255) / 256, 256, 0, s>>>(kb.contact, H, kb.B, dstats, order, (int)stride, cnt);
-  h->launches++;
-  const int nmax = 12 * H;  // largest reduced dimension this horizon can produce
-  // Pass 0 solves every class from the small initial complementarity (kp.z0_scale); the few problems it cannot
-  // solve are collected per class and pass 1 runs the same kernels over those lists with the conservative start.
-  // Both passes are enqueued back to back (the list lengths live on the device): no host synchronisation.
-  const int passes = (mode == 0 && h->kp.z0_scale < 1.0) ? 2 : 1;
-  for (int pass = 0; pass < passes; ++pass) {
-    const bool first = pass == 0;
-    const lmpc::LaunchCtx c{h->device, (first && mode != 2) ? &h->kp : &h->kp_retry, dstats, h->num_sms, s, &h->launches};
-    const int* lst = first ? order : rlist;
-    const int* len = first ? cnt : rcnt;
-    int* wrk = first ? ctr : rctr;
-    auto with_retry = [&](int cls) {  // the batch as class `cls` sees it in this pass
-      KBatch k = kb;
-      k.retry_list = (first && passes == 2) ? rlist + (size_t)cls * stride : nullptr;
-      k.retry_count = (first && passes == 2) ? rcnt + cls : nullptr;
-      if (!first && k.B > 64) k.B = 64;  // (B only caps the grid) a handful of problems: a small grid walks the list
-      return k;
-    };
-    lmpc_status st = LMPC_OK;
-    if (class_mask & 1u)
-      st = h->kp.class0_on_tiles ? lmpc::launch_tile8(c, with_retry(0), &h->d_wsA, lst, len + 0, wrk + 0, 1)
-                                 : lmpc::launch_warp_class(c, with_retry(0), &h->d_wsA, lst, len + 0, wrk + 0);
-    if (st != LMPC_OK) return st;
-    if (nmax > lmpc::kWarpNMax && (class_mask & 2u)) {
-      st = lmpc::launch_tile15(c, with_retry(1), &h->d_wsT1, lst + stride, len + 1, wrk + 1, h->tune.tile_nw);
-      if (st != LMPC_OK) return st;
-    }
-    if (nmax > 8 * lmpc::kTileA && (class_mask & 4u)) {
-      st = lmpc::launch_tile24(c, with_retry(2), &h->d_wsT2, lst + 2 * stride, len + 2, wrk + 2, h->tune.tile_nw);
-      if (st != LMPC_OK) return st;
-    }
-    if (nmax > 8 * lmpc::kTileB && (class_mask & 16u)) {  // class 4 (192 < n <= 288)
-      st = lmpc::launch_tile36(c, with_retry(4), &h->d_wsT3, lst + 4 * stride, len + 4, wrk + 4, 0);
-      if (st != LMPC_OK) return st;
-    }
-    if (nmax > 8 * lmpc::kTileD && (class_mask & 8u)) {  // class 3 (n > 288): only horizons above 24 reach it
-      st = lmpc::launch_tile48(c, with_retry(3), &h->d_ws, lst + 3 * stride, len + 3, wrk + 3, 0);
-      if (st != LMPC_OK) return st;
-    }
+  if (mode == 0 && (h->warm_enabled || h->kp.z0_scale >= 1.0)) mode = 2;
+  if (mode != 4) {
+    CK(cudaMemsetAsync(dstats, 0, sizeof(KStats), s));
+    CK(cudaMemsetAsync(ctr, 0, 4 * lmpc::kCtrCount * sizeof(int), s));
+    CK(cudaEventRecord(h->ev0, s));
+    lmpc::classify_kernel<<<(kb.B + 255) / 256, 256, 0, s>>>(kb.contact, H, kb.B, dstats, order, (int)stride, cnt);
+    h->launches++;
   }
+  const int nmax = 12 * H;  // largest reduced dimension this horizon can produce
+  // Pass 0 solves a class from the small initial complementarity (kp.z0_scale); the few problems it cannot solve
+  // are collected per class and pass 1 runs the same kernel over that list with the conservative start.  Both
+  // passes are enqueued back to back (the list lengths live on the device: no host synchronisation), class by
+  // class, so that consecutive launches keep the same shared-memory configuration (an empty retry launch between
+  // two kernels of different carve-outs measured ~100 us each in the closed loop, profiles/r02_v12_rollout.json).
+  const int pass_lo = mode == 4 ? 1 : 0, pass_hi = (mode == 0 || mode == 4) ? 2 : 1;
+  const bool lists = mode == 0 || mode == 3;  // does the first pass hand its failures over?
+  auto run_class = [&](int cls, auto&& launcher) -> lmpc_status {
+    for (int pass = pass_lo; pass < pass_hi; ++pass) {
+      const bool first = pass == 0;
+      const lmpc::LaunchCtx c{h->device, (first && mode != 2) ? &h->kp : &h->kp_retry, dstats, h->num_sms, s, &h->launches};
+      KBatch k = kb;
+      k.retry_list = (first && lists) ? rlist + (size_t)cls * stride : nullptr;
+      k.retry_count = (first && lists) ? rcnt + cls : nullptr;
+      if (!first && k.B > 256) k.B = 256;  // (B only caps the grid, and above the SM count it does not change the kernel variant) a handful of problems
+      const lmpc_status st = launcher(c, k, (first ? order : rlist) + (size_t)cls * stride, (first ? cnt : rcnt) + cls, (first ? ctr : rctr) + cls);
+      if (st != LMPC_OK) return st;
+    }
+    return LMPC_OK;
+  };
+  using lmpc::LaunchCtx;
+  lmpc_status st = LMPC_OK;
+  if (class_mask & 1u)
+    st = run_class(0, [&](const LaunchCtx& c, const KBatch& k, const int* lst, const int* len, int* wrk) {
+      return h->kp.class0_on_tiles ? lmpc::launch_tile8(c, k, &h->d_wsA, lst, len, wrk, 1) : lmpc::launch_warp_class(c, k, &h->d_wsA, lst, len, wrk);
+    });
+  if (st != LMPC_OK) return st;
+  if (nmax > lmpc::kWarpNMax && (class_mask & 2u))
+    st = run_class(1, [&](const LaunchCtx& c, const KBatch& k, const int* lst, const int* len, int* wrk) {
+      return lmpc::launch_tile15(c, k, &h->d_wsT1, lst, len, wrk, h->tune.tile_nw);
+    });
+  if (st != LMPC_OK) return st;
+  if (nmax > 8 * lmpc::kTileA && (class_mask & 4u))
+    st = run_class(2, [&](const LaunchCtx& c, const KBatch& k, const int* lst, const int* len, int* wrk) {
+      return lmpc::launch_tile24(c, k, &h->d_wsT2, lst, len, wrk, h->tune.tile_nw);
+    });
+  if (st != LMPC_OK) return st;
+  if (nmax > 8 * lmpc::kTileB && (class_mask & 16u))  // class 4 (192 < n <= 288)
+    st = run_class(4, [&](const LaunchCtx& c, const KBatch& k, const int* lst, const int* len, int* wrk) {
+      return lmpc::launch_tile36(c, k, &h->d_wsT3, lst, len, wrk, 0);
+    });
+  if (st != LMPC_OK) return st;
+  if (nmax > 8 * lmpc::kTileD && (class_mask & 8u))  // class 3 (n > 288): only horizons above 24 reach it
+    st = run_class(3, [&](const LaunchCtx& c, const KBatch& k, const int* lst, const int* len, int* wrk) {
+      return lmpc::launch_tile48(c, k, &h->d_ws, lst, len, wrk, 0);
+    });
+  if (st != LMPC_OK) return st;
   CK(cudaEventRecord(h->ev1, s));
   return LMPC_OK;
+}
+
+// Blocking two-pass solve: first pass, look at the statistics, retry pass only if something was handed over.
+// Leaves the kernels finished or enqueued on `s`; the caller copies results out and calls finish_solve.
+static lmpc_status solve_passes_blocking(lmpc_handle* h, const KBatch& kb, cudaStream_t s, unsigned class_mask = ~0u) {
+  if (h->warm_enabled || h->kp.z0_scale >= 1.0) return launch_solve(h, kb, s, class_mask, 2);
+  lmpc_status st = launch_solve(h, kb, s, class_mask, 3);
+  if (st != LMPC_OK) return st;
+  CK(cudaMemcpyAsync(&h->last_stats, h->d_stats.p, sizeof(KStats), cudaMemcpyDeviceToHost, s));
+  CK(cudaStreamSynchronize(s));
+  if (h->last_stats.handed > 0) st = launch_solve(h, kb, s, class_mask, 4);
+  return st;
 }
 
 static lmpc_status finish_solve(lmpc_handle* h, cudaStream_t s) {
@@ -341,7 +371,7 @@ extern "C" lmpc_status lmpc_solve(lmpc_handle* h, int32_t batch, const lmpc_batc
   CK(cudaSetDevice(h->device));
   cudaStream_t s = h->stream;
   if (in->on_device) {
-    st = launch_solve(h, device_batch(in, out, batch), s);
+    st = solve_passes_blocking(h, device_batch(in, out, batch), s);
     if (st != LMPC_OK) return st;
     return finish_solve(h, s);
   }
@@ -440,7 +470,7 @@ extern "C" lmpc_status lmpc_solve(lmpc_handle* h, int32_t batch, const lmpc_batc
   kb.iters = out->iters ? (int*)h->d_iters.p : nullptr; kb.active = out->active_set ? (uint32_t*)h->d_active.p : nullptr;
   kb.U = out->U ? (double*)h->d_U.p : nullptr; kb.order = nullptr; kb.B = batch;
   kb.warm = nullptr; kb.warm_shift = 0;
-  st = launch_solve(h, kb, s);
+  st = solve_passes_blocking(h, kb, s);
   if (st != LMPC_OK) return st;
   CK(cudaMemcpyAsync(out->grf, kb.grf, B * 12 * 8, cudaMemcpyDeviceToHost, s));
   if (out->status) CK(cudaMemcpyAsync(out->status, kb.status, B * 4, cudaMemcpyDeviceToHost, s));

@@ -886,6 +886,7 @@ __device__ void solve_one_tile(const KParams& P, const KBatch& Bt, WarpStats& ws
     // whose outputs replace the zeros written above; it is counted there
     const bool handed = status >= 2 && Bt.retry_list != nullptr;
     if (handed && lane == 0) Bt.retry_list[atomicAdd(Bt.retry_count, 1)] = pi;
+    if (handed) ws.handed++;
     if (!handed) { ws.problems++; ws.sum_n += n; }
     ws.sum_fact += nf; ws.sum_polish += n_polish;
     if (status >= 2 && !handed) ws.not_ok++;

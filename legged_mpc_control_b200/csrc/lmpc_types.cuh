@@ -89,6 +89,7 @@ struct KStats {
   unsigned long long not_ok;       // problems with status >= 2
   unsigned long long ipm_only;     // problems with status == 1
   unsigned long long warm_hits;    // problems solved from the stored faces alone (no interior-point iteration)
+  unsigned long long handed;       // problems the first pass handed to the retry pass (KBatch::retry_list)
   double flops;                    // executed factorization+solve flops (n^3/3 + 4n^2 per factorization etc.)
   int n_max;                       // max reduced dimension seen by the classify pass
 };

@@ -49,12 +49,12 @@ __host__ __device__ inline WarpPlan make_warp_plan(int H) {
 }
 
 struct WarpStats {
-  unsigned long long problems = 0, sum_n = 0, sum_fact = 0, sum_polish = 0, not_ok = 0, ipm_only = 0, warm_hits = 0;
+  unsigned long long problems = 0, sum_n = 0, sum_fact = 0, sum_polish = 0, not_ok = 0, ipm_only = 0, warm_hits = 0, handed = 0;
   double flops = 0;
 };
 
 __device__ inline void flush_warp_stats(const WarpStats& ws, KStats* stats) {
-  if ((threadIdx.x & 31) == 0 && ws.problems) {
+  if ((threadIdx.x & 31) == 0 && (ws.problems | ws.handed | ws.sum_fact)) {  // (a warp may have handed over everything it touched)
     atomicAdd(&stats->problems, ws.problems);
     atomicAdd(&stats->sum_n, ws.sum_n);
     atomicAdd(&stats->sum_fact, ws.sum_fact);
@@ -62,6 +62,7 @@ __device__ inline void flush_warp_stats(const WarpStats& ws, KStats* stats) {
     if (ws.not_ok) atomicAdd(&stats->not_ok, ws.not_ok);
     if (ws.ipm_only) atomicAdd(&stats->ipm_only, ws.ipm_only);
     if (ws.warm_hits) atomicAdd(&stats->warm_hits, ws.warm_hits);
+    if (ws.handed) atomicAdd(&stats->handed, ws.handed);
     atomicAdd(&stats->flops, ws.flops);
   }
 }
@@ -804,6 +805,7 @@ static __device__ void solve_one_warp(const KParams& P, const KBatch& Bt, WarpSt
     // whose outputs replace the zeros written above; it is counted there
     const bool handed = status >= 2 && Bt.retry_list != nullptr;
     if (handed && lane == 0) Bt.retry_list[atomicAdd(Bt.retry_count, 1)] = pi;
+    if (handed) ws.handed++;
     if (!handed) { ws.problems++; ws.sum_n += n; }
     ws.sum_fact += nf; ws.sum_polish += n_polish;
     if (status >= 2 && !handed) ws.not_ok++;
