@@ -522,7 +522,7 @@ def _parity(p, kept, tout, n):
             "status_counts": np.bincount(got["status"], minlength=4).tolist(), "tolerance": pu.REL_TOL}
 
 
-NCU_TRAFFIC_FILE = "r02_v10_ncu_full_solve_warp_kernel.csv"  # one 65 536-problem launch of the headline workload, `ncu --set full`
+NCU_TRAFFIC_FILE = "r02_v13_ncu_full_solve_warp_kernel.csv"  # one 65 536-problem launch of the headline workload, `ncu --set full`
 
 
 def _ncu_traffic():

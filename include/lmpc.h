@@ -172,7 +172,13 @@ lmpc_status lmpc_solve(lmpc_handle* h, int32_t batch, const lmpc_batch_in* in,
                        const lmpc_batch_out* out);
 
 /* Asynchronous variant on the handle's stream (or `cuda_stream` if non-NULL: a cudaStream_t).
- * Only valid with on_device inputs and outputs.  lmpc_wait blocks until it is done. */
+ * Only valid with on_device inputs and outputs.  lmpc_wait blocks until it is done.
+ * Everything the call needs is enqueued before it returns (classification, the solve kernels of every size
+ * class the horizon can produce, and — cold engines — a second launch of the same kernels over the few problems
+ * the first pass handed back: the interior point starts from a small complementarity, and what that start does
+ * not carry to an answer is solved again from the classical one), so work queued behind it on the same stream
+ * sees complete results.  The blocking lmpc_solve looks at the first pass's statistics instead and launches the
+ * second pass only when something was handed back. */
 lmpc_status lmpc_solve_async(lmpc_handle* h, int32_t batch, const lmpc_batch_in* in,
                              const lmpc_batch_out* out, void* cuda_stream);
 lmpc_status lmpc_wait(lmpc_handle* h);
@@ -195,7 +201,8 @@ lmpc_status lmpc_wait(lmpc_handle* h);
  * start is not used and lmpc_last_* / lmpc_wait do not see this call.
  * blocking != 0: waits for the result and returns LMPC_ERR_NOT_CONVERGED if any problem ended with
  * status >= 2; blocking == 0: returns after the launch, the caller synchronises the stream and reads
- * status[].  Results are the same exact minimisers lmpc_solve returns.
+ * status[].  Results are the same exact minimisers lmpc_solve returns (one launch from the classical
+ * interior-point start: iteration counts differ from lmpc_solve's, answers do not).
  * ALL calls on a device share the one array, which keeps the previous call's contents (the call
  * clears the part that must start at zero): two calls that overlap on the GPU — different streams,
  * or two host threads — race.  Serialise them. */
