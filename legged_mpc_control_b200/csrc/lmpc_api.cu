@@ -87,7 +87,7 @@ static void fill_kparams(const lmpc_params& p, KParams* k) {
   k->cs = p.cost_scaling == LMPC_COST_NS_TWO ? 2.0 : 1.0;
   k->act_tol = p.active_tol > 0 ? p.active_tol : 1e-6;
   // solver tuning (environment overrides are for experiments only)
-  k->tol0 = 1e-7; k->rdtol0 = 1e-9; k->fz0 = 0.0;
+  k->tol0 = 1e-7; k->rdtol0 = 1e-7; k->fz0 = 0.0;  // hand-over to the polish: swept with the small-complementarity start (tools/gpu_r2_tol0.sh): rdtol0 1e-9 -> 1e-7 is +0.7 % (H=10) ... +4 % (H=30 trot)
   if (const char* e = getenv("LMPC_TOL0")) k->tol0 = atof(e);
   if (const char* e = getenv("LMPC_RDTOL0")) k->rdtol0 = atof(e);
   if (const char* e = getenv("LMPC_FZ0")) k->fz0 = atof(e);
