@@ -395,6 +395,9 @@ def run_b200(args):
                 "fp64_peaks_tflops": peaks,
                 "flops_per_launch_executed": stats["flops_executed"], "mean_n_eff": stats["mean_n_eff"],
                 "mean_factorizations": Kf, "alg_flops_per_solve_dense_n12H": f_alg_dense,
+                "note": "achieved counts the flops the kernel executes; the round-2 interior-point start needs 7.6 instead of 10.9 "
+                        "factorizations per solve (round 1), i.e. ~30 % fewer executed flops per solve in ~16 % less time, so frac falls "
+                        "while solves/s (the metric) rises; per-solve set-up, polish and instruction fetch are the remaining cost (DESIGN.md 6)",
                 "hbm": {"algorithmic_bytes_per_launch": io_bytes, "achieved_GBps": io_bytes / (kms * 1e-3) / 1e9,
                         "peak_GBps": _hbm_peak()},
             },
