@@ -122,6 +122,11 @@ static lmpc_status create_resources(lmpc_handle* h) {
   CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
   CK(cudaEventCreate(&h->ev0));
   CK(cudaEventCreate(&h->ev1));
+  CK(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
+  for (int c = 1; c < lmpc::kNumClasses; ++c) {
+    CK(cudaStreamCreateWithFlags(&h->side[c], cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&h->ev_join[c], cudaEventDisableTiming));
+  }
   CK(h->d_stats.ensure(sizeof(KStats)));
   CK(h->d_counter.ensure(4 * lmpc::kCtrCount * sizeof(int)));  // work counters, class sizes, and the same two for the retry launches
   CK(h->d_retry.ensure(lmpc::kNumClasses * (size_t)h->max_batch * sizeof(int)));
@@ -162,6 +167,7 @@ extern "C" lmpc_status lmpc_create(const lmpc_params* params, int32_t max_batch,
   if (const char* e = getenv("LMPC_TILE_NW")) h->tune.tile_nw = atoi(e);
   h->tune.debug_stats = getenv("LMPC_DEBUG_STATS") != nullptr;
   if (const char* e = getenv("LMPC_HOST_LANES")) h->tune.host_lanes = atoi(e);
+  if (const char* e = getenv("LMPC_FORK_CLASSES")) h->tune.fork_classes = atoi(e) != 0;
   memset(&h->last_stats, 0, sizeof(KStats));
   if (h->kp.l2_persist) {
     cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)prop.persistingL2CacheMaxSize);
@@ -196,6 +202,11 @@ extern "C" void lmpc_destroy(lmpc_handle* h) {
   if (h->ev1) cudaEventDestroy(h->ev1);
   if (h->ev_r0) cudaEventDestroy(h->ev_r0);
   if (h->ev_r1) cudaEventDestroy(h->ev_r1);
+  if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+  for (int c = 1; c < lmpc::kNumClasses; ++c) {
+    if (h->side[c]) { cudaStreamSynchronize(h->side[c]); cudaStreamDestroy(h->side[c]); }
+    if (h->ev_join[c]) cudaEventDestroy(h->ev_join[c]);
+  }
   if (h->h_pin) cudaFreeHost(h->h_pin);
   if (h->h_pout) cudaFreeHost(h->h_pout);
   if (h->stream) cudaStreamDestroy(h->stream);
@@ -237,6 +248,8 @@ static lmpc_status launch_solve(lmpc_handle* h, KBatch kb, cudaStream_t s, unsig
     lmpc::classify_kernel<<<(kb.B + 255) / 256, 256, 0, s>>>(kb.contact, H, kb.B, dstats, order, (int)stride, cnt);
     h->launches++;
   }
+  const bool fork = h->tune.fork_classes;
+  if (fork) CK(cudaEventRecord(h->ev_fork, s));  // everything the class kernels read is enqueued on `s` before this point
   const int nmax = 12 * H;  // largest reduced dimension this horizon can produce
   // Pass 0 solves a class from the small initial complementarity (kp.z0_scale); the few problems it cannot solve
   // are collected per class and pass 1 runs the same kernel over that list with the conservative start.  Both
@@ -246,15 +259,22 @@ static lmpc_status launch_solve(lmpc_handle* h, KBatch kb, cudaStream_t s, unsig
   const int pass_lo = mode == 4 ? 1 : 0, pass_hi = (mode == 0 || mode == 4) ? 2 : 1;
   const bool lists = mode == 0 || mode == 3;  // does the first pass hand its failures over?
   auto run_class = [&](int cls, auto&& launcher) -> lmpc_status {
+    const bool side = fork && cls > 0;
+    cudaStream_t cs = side ? h->side[cls] : s;
+    if (side) CK(cudaStreamWaitEvent(cs, h->ev_fork, 0));
     for (int pass = pass_lo; pass < pass_hi; ++pass) {
       const bool first = pass == 0;
-      const lmpc::LaunchCtx c{h->device, (first && mode != 2) ? &h->kp : &h->kp_retry, dstats, h->num_sms, s, &h->launches};
+      const lmpc::LaunchCtx c{h->device, (first && mode != 2) ? &h->kp : &h->kp_retry, dstats, h->num_sms, cs, &h->launches};
       KBatch k = kb;
       k.retry_list = (first && lists) ? rlist + (size_t)cls * stride : nullptr;
       k.retry_count = (first && lists) ? rcnt + cls : nullptr;
       if (!first && k.B > 256) k.B = 256;  // (B only caps the grid, and above the SM count it does not change the kernel variant) a handful of problems
       const lmpc_status st = launcher(c, k, (first ? order : rlist) + (size_t)cls * stride, (first ? cnt : rcnt) + cls, (first ? ctr : rctr) + cls);
       if (st != LMPC_OK) return st;
+    }
+    if (side) {  // join: the call's stream (and its end event) waits for this class
+      CK(cudaEventRecord(h->ev_join[cls], cs));
+      CK(cudaStreamWaitEvent(s, h->ev_join[cls], 0));
     }
     return LMPC_OK;
   };

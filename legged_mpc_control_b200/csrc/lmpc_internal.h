@@ -81,6 +81,7 @@ lmpc_status launch_tile48(const LaunchCtx& c, const KBatch& kb, DevBuf* ws, cons
 struct Tuning {
   int tile_nw = 0;        // LMPC_TILE_NW: warps per QP of tile classes 1/2 (0 = measured default)
   bool debug_stats = false;  // LMPC_DEBUG_STATS: print per-solve counters to stderr
+  bool fork_classes = true;  // LMPC_FORK_CLASSES=0: all size classes on the call's stream, one after the other
   int host_lanes = 4;     // LMPC_HOST_LANES: slices of a large host-pointer batch in flight (copy/solve overlap); <= 1 = off
 };
 
@@ -97,6 +98,11 @@ struct lmpc_handle {
   lmpc::DevBuf d_x0, d_rot, d_foot, d_cmd, d_contact, d_q, d_r, d_mu, d_fz, d_mass, d_inertia;
   lmpc::DevBuf d_grf, d_status, d_iters, d_active, d_U;
   lmpc::DevBuf d_stats, d_counter, d_ws, d_wsA, d_wsT1, d_wsT2, d_wsT3, d_order, d_warm;
+  // Size classes 1.. launch on side streams forked from the call's stream after the classification and joined
+  // before its end event: their lists are independent, so an empty (or short) class runs beside the one that has
+  // the work instead of adding its launch latency behind it.
+  cudaStream_t side[lmpc::kNumClasses] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t ev_fork = nullptr, ev_join[lmpc::kNumClasses] = {nullptr, nullptr, nullptr, nullptr, nullptr};
   lmpc::DevBuf d_retry;     // per size class: the problems the first launch handed to the retry launch (KBatch::retry_list)
   lmpc::KParams kp_retry;   // kp with the conservative interior-point start (z0_scale = 1)
   bool warm_enabled = false;
