@@ -178,7 +178,9 @@ lmpc_status lmpc_solve(lmpc_handle* h, int32_t batch, const lmpc_batch_in* in,
  * the first pass handed back: the interior point starts from a small complementarity, and what that start does
  * not carry to an answer is solved again from the classical one), so work queued behind it on the same stream
  * sees complete results.  The blocking lmpc_solve looks at the first pass's statistics instead and launches the
- * second pass only when something was handed back. */
+ * second pass only when something was handed back.  Size classes beyond the first run on streams of the handle
+ * that are forked from this stream after the classification and joined back into it before the call's end, so
+ * stream order as the caller sees it is unchanged. */
 lmpc_status lmpc_solve_async(lmpc_handle* h, int32_t batch, const lmpc_batch_in* in,
                              const lmpc_batch_out* out, void* cuda_stream);
 lmpc_status lmpc_wait(lmpc_handle* h);
