@@ -253,9 +253,10 @@ static lmpc_status launch_solve(lmpc_handle* h, KBatch kb, cudaStream_t s, unsig
   const int nmax = 12 * H;  // largest reduced dimension this horizon can produce
   // Pass 0 solves a class from the small initial complementarity (kp.z0_scale); the few problems it cannot solve
   // are collected per class and pass 1 runs the same kernel over that list with the conservative start.  Both
-  // passes are enqueued back to back (the list lengths live on the device: no host synchronisation), class by
-  // class, so that consecutive launches keep the same shared-memory configuration (an empty retry launch between
-  // two kernels of different carve-outs measured ~100 us each in the closed loop, profiles/r02_v12_rollout.json).
+  // passes are enqueued back to back on the class's stream (the list lengths live on the device: no host
+  // synchronisation).  An empty launch behind a persistent grid costs ~75 us of stream time (not the kernel: it runs
+  // 3.5 us; neither its grid nor the order of the launches changes that), which is why blocking calls enqueue pass 1
+  // only on demand (modes 3 / 4) and why the classes run on forked streams.
   const int pass_lo = mode == 4 ? 1 : 0, pass_hi = (mode == 0 || mode == 4) ? 2 : 1;
   const bool lists = mode == 0 || mode == 3;  // does the first pass hand its failures over?
   auto run_class = [&](int cls, auto&& launcher) -> lmpc_status {
